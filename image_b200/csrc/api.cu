@@ -1,0 +1,450 @@
+// api.cu -- the extern "C" surface of libb200img (include/b200img.h): argument
+// checking in the reference's terms, per-device context and scratch, and the
+// host-pointer wrappers (H2D -> kernels -> D2H) around the device entry points.
+#include "common.cuh"
+#include "host_tables.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace b200 {
+
+// implemented in the kernel files
+int convert_dev(const void *src, int sd, int cin, void *dst, int dd, int cout, size_t n, int mode,
+                const float coefs[3], int fused_mac, cudaStream_t st);
+int swizzle_dev(void *buf, int dtype, int channels, size_t nsub, cudaStream_t st);
+int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h,
+                  int C, int dtype, void *dst, size_t dst_stride, uint32_t dst_row0, uint32_t dst_rows,
+                  uint32_t nw, uint32_t nh, uint32_t n_images, int filter, float acc_init, int flags,
+                  cudaStream_t st);
+int resize_band_src_rows(uint32_t h, uint32_t nh, int filter, uint32_t dst_row0, uint32_t dst_rows,
+                         uint32_t *src_row0, uint32_t *src_rows);
+void resize_release_tables(int device);
+int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
+                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st);
+int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
+                     float sigma, cudaStream_t st);
+
+// ---- errors -------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+int fail(int status, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return status;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    snprintf(g_err, sizeof g_err, "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    cudaGetLastError();  // clear the sticky-less error state
+    return e == cudaErrorMemoryAllocation ? B200IMG_ERR_OOM : B200IMG_ERR_CUDA;
+}
+
+bool checked_mul(size_t a, size_t b, size_t c, size_t d, size_t *out) {
+    size_t r;
+    if (__builtin_mul_overflow(a, b, &r) || __builtin_mul_overflow(r, c, &r) || __builtin_mul_overflow(r, d, &r)) return false;
+    *out = r;
+    return true;
+}
+
+// ---- per-device context -------------------------------------------------------
+static std::mutex g_ctx_mu;
+static std::map<int, DeviceCtx> g_ctx;
+
+DeviceCtx *current_ctx() {
+    int dev;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaGetDevice (is there a GPU? libb200img has no CPU fallback)");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    auto it = g_ctx.find(dev);
+    if (it != g_ctx.end()) return &it->second;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, dev);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaGetDeviceProperties");
+        return nullptr;
+    }
+    if (prop.major < 10) {
+        fail(B200IMG_ERR_CUDA, "device %d is sm_%d%d; libb200img is built for sm_100a only", dev, prop.major, prop.minor);
+        return nullptr;
+    }
+    DeviceCtx c;
+    c.device = dev;
+    c.sm_count = prop.multiProcessorCount;
+    c.smem_optin = prop.sharedMemPerBlockOptin;
+    return &(g_ctx[dev] = c);
+}
+
+// ---- scratch pool: one buffer per (device, stream, slot), grown on demand -----------
+struct ScratchBuf { void *p = nullptr; size_t bytes = 0; };
+static std::mutex g_scr_mu;
+static std::map<std::tuple<int, cudaStream_t, int>, ScratchBuf> g_scr;
+static thread_local cudaStream_t g_scratch_stream = nullptr;
+
+void set_scratch_stream(cudaStream_t st) { g_scratch_stream = st; }
+
+int scratch(ScratchSlot slot, size_t bytes, void **out) {
+    int dev;
+    B200_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_scr_mu);
+    ScratchBuf &b = g_scr[std::make_tuple(dev, g_scratch_stream, (int)slot)];
+    if (b.bytes < bytes) {
+        if (b.p) cudaFree(b.p);  // synchronises: queued kernels that use it have finished
+        b.p = nullptr; b.bytes = 0;
+        const size_t want = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+        cudaError_t e = cudaMalloc(&b.p, want);
+        if (e != cudaSuccess) {
+            b.p = nullptr;
+            cudaGetLastError();
+            return fail(B200IMG_ERR_OOM, "cannot allocate %zu bytes of device scratch", want);
+        }
+        b.bytes = want;
+    }
+    *out = b.p;
+    return B200IMG_OK;
+}
+
+static void release_scratch(int dev) {
+    std::lock_guard<std::mutex> lk(g_scr_mu);
+    for (auto it = g_scr.begin(); it != g_scr.end();) {
+        if (std::get<0>(it->first) == dev) { cudaFree(it->second.p); it = g_scr.erase(it); }
+        else ++it;
+    }
+}
+
+static std::mutex g_host_api_mu;  // host-pointer entry points share the stream-0 scratch
+
+// RAII: host-pointer call = lock, device buffers, copy in ... copy out, sync
+struct HostCall {
+    std::lock_guard<std::mutex> lk;
+    HostCall() : lk(g_host_api_mu) { set_scratch_stream(nullptr); }
+    int in(const void *h, size_t bytes, void **d) {
+        int rc = scratch(SCRATCH_IO_SRC, bytes ? bytes : 1, d);
+        if (rc) return rc;
+        if (bytes) B200_CUDA(cudaMemcpyAsync(*d, h, bytes, cudaMemcpyHostToDevice, 0));
+        return B200IMG_OK;
+    }
+    int out_buf(size_t bytes, void **d) { return scratch(SCRATCH_IO_DST, bytes ? bytes : 1, d); }
+    int out(void *h, const void *d, size_t bytes) {
+        if (bytes) B200_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, 0));
+        B200_CUDA(cudaStreamSynchronize(0));
+        return B200IMG_OK;
+    }
+};
+
+static int check_image(const char *op, int channels, int dtype, uint32_t w, uint32_t h, size_t *bytes) {
+    if (channels < 1 || channels > 4) return fail(B200IMG_ERR_BAD_ARG, "%s: channels must be 1..4 (got %d)", op, channels);
+    if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "%s: bad dtype %d", op, dtype);
+    if (!checked_mul(w, h, (size_t)channels, dtype_size(dtype), bytes))
+        return fail(B200IMG_ERR_DIMENSION, "%s: image size overflows", op);
+    return B200IMG_OK;
+}
+
+// imageops::resize front end (src/imageops/sample.rs:970-991): the two early-outs
+static int resize_front(const void *src, size_t src_stride, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                        size_t dst_stride, uint32_t nw, uint32_t nh, uint32_t n, int filter, float acc_init,
+                        int flags, cudaStream_t st) {
+    size_t sb, db;
+    int rc = check_image("resize", C, dtype, w, h, &sb);
+    if (rc) return rc;
+    rc = check_image("resize", C, dtype, nw, nh, &db);
+    if (rc) return rc;
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize: unknown filter %d", filter);
+    if (n == 0 || db == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "resize: null buffer");
+    if (!src_stride) src_stride = sb;
+    if (!dst_stride) dst_stride = db;
+    if (w == 0 || h == 0) {  // nothing to sample from: zero-filled buffer
+        B200_CUDA(cudaMemset2DAsync(dst, dst_stride, 0, db, n, st));
+        return B200IMG_OK;
+    }
+    if (nw == w && nh == h) {  // same dimensions: a copy
+        B200_CUDA(cudaMemcpy2DAsync(dst, dst_stride, src, src_stride, sb, n, cudaMemcpyDeviceToDevice, st));
+        return B200IMG_OK;
+    }
+    set_scratch_stream(st);
+    return resize_launch(src, src_stride, 0, h, w, h, C, dtype, dst, dst_stride, 0, nh, nw, nh, n, filter, acc_init, flags, st);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+const char *b200img_last_error(void) { return g_err; }
+int b200img_version(void) { return 100; }
+
+int b200img_device_count(int *count) {
+    if (!count) return fail(B200IMG_ERR_BAD_ARG, "device_count: null pointer");
+    B200_CUDA(cudaGetDeviceCount(count));
+    return B200IMG_OK;
+}
+
+int b200img_pinned_alloc(size_t bytes, void **out) {
+    if (!out) return fail(B200IMG_ERR_BAD_ARG, "pinned_alloc: null pointer");
+    cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(B200IMG_ERR_OOM, "pinned_alloc: %s", cudaGetErrorString(e)); }
+    return B200IMG_OK;
+}
+int b200img_pinned_free(void *p) {
+    if (p) B200_CUDA(cudaFreeHost(p));
+    return B200IMG_OK;
+}
+
+int b200img_release_caches(void) {
+    int dev;
+    B200_CUDA(cudaGetDevice(&dev));
+    B200_CUDA(cudaDeviceSynchronize());
+    release_scratch(dev);
+    resize_release_tables(dev);
+    return B200IMG_OK;
+}
+
+// ---- host tables --------------------------------------------------------------
+float b200img_filter_support(int filter) { return filter_support(filter); }
+float b200img_filter_kernel(int filter, float x) { return filter_kernel(filter, x); }
+
+int b200img_resize_max_taps(int filter, uint32_t src_len, uint32_t dst_len) {
+    if (filter_support(filter) < 0 || dst_len == 0) return fail(B200IMG_ERR_BAD_ARG, "resize_max_taps: bad argument");
+    return resize_max_taps(filter, src_len, dst_len);
+}
+
+int b200img_build_weights(int filter, uint32_t src_len, uint32_t dst_len, int axis, int32_t *left, int32_t *count,
+                          float *weights, int stride) {
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "build_weights: unknown filter %d", filter);
+    if (src_len == 0) return fail(B200IMG_ERR_BAD_ARG, "build_weights: empty source axis");
+    if (axis != 0 && axis != 1) return fail(B200IMG_ERR_BAD_ARG, "build_weights: axis must be 0 (vertical) or 1 (horizontal)");
+    if (dst_len == 0) return B200IMG_OK;
+    if (!left || !count || !weights) return fail(B200IMG_ERR_BAD_ARG, "build_weights: null pointer");
+    AxisTable t;
+    build_axis_table(filter, src_len, dst_len, axis, t);
+    if (t.max_count > stride) return fail(B200IMG_ERR_BAD_ARG, "build_weights: stride %d < %d taps", stride, t.max_count);
+    for (uint32_t o = 0; o < dst_len; ++o) {
+        left[o] = t.left[o];
+        count[o] = t.count[o];
+        for (int i = 0; i < stride; ++i) weights[(size_t)o * stride + i] = i < t.count[o] ? t.w[(size_t)o * t.stride + i] : 0.0f;
+    }
+    return B200IMG_OK;
+}
+
+int b200img_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill, uint32_t *ow, uint32_t *oh) {
+    if (!ow || !oh) return fail(B200IMG_ERR_BAD_ARG, "resize_dimensions: null pointer");
+    resize_dimensions(w, h, nw, nh, fill != 0, ow, oh);
+    return B200IMG_OK;
+}
+
+#define PARAMS_FN(name, call)                                                                          \
+    {                                                                                                  \
+        if (!out) return fail(B200IMG_ERR_BAD_ARG, name ": null pointer");                             \
+        int rc = call;                                                                                 \
+        if (rc) return fail(rc, name ": invalid argument (the reference asserts here)");               \
+        return B200IMG_OK;                                                                             \
+    }
+int b200img_gauss_params_from_radius(float r, b200img_gauss_params *out) PARAMS_FN("gauss_params_from_radius", gauss_params_from_radius(r, out))
+int b200img_gauss_params_from_kernel_size(float k, b200img_gauss_params *out) PARAMS_FN("gauss_params_from_kernel_size", gauss_params_from_kernel_size(k, out))
+int b200img_gauss_params_from_anisotropic(float x, float y, b200img_gauss_params *out) PARAMS_FN("gauss_params_from_anisotropic", gauss_params_from_anisotropic(x, y, out))
+int b200img_gauss_params_from_sigma(float s, b200img_gauss_params *out) PARAMS_FN("gauss_params_from_sigma", gauss_params_from_sigma(s, out))
+#undef PARAMS_FN
+
+int b200img_gaussian_kernel_1d(uint32_t width, float sigma, float *out) {
+    if (!out && width) return fail(B200IMG_ERR_BAD_ARG, "gaussian_kernel_1d: null pointer");
+    std::vector<float> k = gaussian_kernel_1d(width, sigma);
+    memcpy(out, k.data(), k.size() * sizeof(float));
+    return B200IMG_OK;
+}
+
+int b200img_boxes_for_gauss(float sigma, uint32_t out[3]) {
+    if (!out) return fail(B200IMG_ERR_BAD_ARG, "boxes_for_gauss: null pointer");
+    boxes_for_gauss(sigma, out);
+    return B200IMG_OK;
+}
+
+// ---- resampler ----------------------------------------------------------------
+int b200img_resize_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                       int filter, float acc_init, int flags, void *stream) {
+    return resize_front(src, 0, w, h, C, dtype, dst, 0, nw, nh, 1, filter, acc_init, flags, (cudaStream_t)stream);
+}
+
+int b200img_resize_batch_dev(const void *src, size_t src_stride, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                             size_t dst_stride, uint32_t nw, uint32_t nh, uint32_t n, int filter, float acc_init,
+                             int flags, void *stream) {
+    return resize_front(src, src_stride, w, h, C, dtype, dst, dst_stride, nw, nh, n, filter, acc_init, flags, (cudaStream_t)stream);
+}
+
+int b200img_resize(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                   int filter, float acc_init, int flags) {
+    size_t sb, db;
+    int rc = check_image("resize", C, dtype, w, h, &sb);
+    if (rc) return rc;
+    rc = check_image("resize", C, dtype, nw, nh, &db);
+    if (rc) return rc;
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize: unknown filter %d", filter);
+    if (db == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "resize: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, sb, &ds))) return rc;
+    if ((rc = hc.out_buf(db, &dd))) return rc;
+    if ((rc = resize_front(ds, 0, w, h, C, dtype, dd, 0, nw, nh, 1, filter, acc_init, flags, 0))) return rc;
+    return hc.out(dst, dd, db);
+}
+
+int b200img_resize_band_src_rows(uint32_t h, uint32_t nh, int filter, uint32_t dst_row0, uint32_t dst_rows,
+                                 uint32_t *src_row0, uint32_t *src_rows) {
+    if (!src_row0 || !src_rows) return fail(B200IMG_ERR_BAD_ARG, "resize_band_src_rows: null pointer");
+    return resize_band_src_rows(h, nh, filter, dst_row0, dst_rows, src_row0, src_rows);
+}
+
+int b200img_resize_band_dev(const void *src_band, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h, int C,
+                            int dtype, void *dst_band, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh,
+                            int filter, float acc_init, int flags, void *stream) {
+    size_t sb, db;
+    int rc = check_image("resize_band", C, dtype, w, h, &sb);
+    if (rc) return rc;
+    rc = check_image("resize_band", C, dtype, nw, nh, &db);
+    if (rc) return rc;
+    if (w == 0 || h == 0 || nw == 0 || nh == 0) return fail(B200IMG_ERR_BAD_ARG, "resize_band: empty image");
+    if (dst_rows == 0) return B200IMG_OK;
+    if (dst_row0 + (uint64_t)dst_rows > nh || src_row0 + (uint64_t)src_rows > h)
+        return fail(B200IMG_ERR_BAD_ARG, "resize_band: band outside the image");
+    if (!src_band || !dst_band) return fail(B200IMG_ERR_BAD_ARG, "resize_band: null buffer");
+    set_scratch_stream((cudaStream_t)stream);
+    return resize_launch(src_band, 0, src_row0, src_rows, w, h, C, dtype, dst_band, 0, dst_row0, dst_rows, nw, nh, 1,
+                         filter, acc_init, flags, (cudaStream_t)stream);
+}
+
+// ---- Gaussian blur ------------------------------------------------------------
+static int gauss_check(const b200img_gauss_params *p, int path) {
+    if (!p) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: null params");
+    if (path != B200IMG_BLUR_GENERIC && path != B200IMG_BLUR_DYN) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: bad path %d", path);
+    // filter_2d_separable asserts odd lengths (src/imageops/filter_1d.rs:649-654)
+    if ((p->x_kernel_size & 1u) == 0 || (p->y_kernel_size & 1u) == 0)
+        return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: kernel sizes must be odd (%u, %u)", p->x_kernel_size, p->y_kernel_size);
+    return B200IMG_OK;
+}
+
+int b200img_gaussian_blur_batch_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n,
+                                    const b200img_gauss_params *p, int path, int flags, void *stream) {
+    size_t bytes;
+    int rc = check_image("gaussian_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if ((rc = gauss_check(p, path))) return rc;
+    if (bytes == 0 || n == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: null buffer");
+    set_scratch_stream((cudaStream_t)stream);
+    return gaussian_blur_launch(src, w, h, C, dtype, dst, n, p, path, flags, (cudaStream_t)stream);
+}
+
+int b200img_gaussian_blur_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                              const b200img_gauss_params *p, int path, int flags, void *stream) {
+    return b200img_gaussian_blur_batch_dev(src, w, h, C, dtype, dst, 1, p, path, flags, stream);
+}
+
+int b200img_gaussian_blur(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                          const b200img_gauss_params *p, int path, int flags) {
+    size_t bytes;
+    int rc = check_image("gaussian_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if ((rc = gauss_check(p, path))) return rc;
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    if ((rc = hc.out_buf(bytes, &dd))) return rc;
+    if ((rc = gaussian_blur_launch(ds, w, h, C, dtype, dd, 1, p, path, flags, 0))) return rc;
+    return hc.out(dst, dd, bytes);
+}
+
+// ---- fast_blur ----------------------------------------------------------------
+int b200img_fast_blur_batch_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n,
+                                float sigma, void *stream) {
+    size_t bytes;
+    int rc = check_image("fast_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0 || n == 0) return B200IMG_OK;  // empty image: clone (fast_blur.rs:117-119)
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "fast_blur: null buffer");
+    set_scratch_stream((cudaStream_t)stream);
+    return fast_blur_launch(src, w, h, C, dtype, dst, n, sigma, (cudaStream_t)stream);
+}
+
+int b200img_fast_blur_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float sigma, void *stream) {
+    return b200img_fast_blur_batch_dev(src, w, h, C, dtype, dst, 1, sigma, stream);
+}
+
+int b200img_fast_blur(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float sigma) {
+    size_t bytes;
+    int rc = check_image("fast_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "fast_blur: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    if ((rc = hc.out_buf(bytes, &dd))) return rc;
+    if ((rc = fast_blur_launch(ds, w, h, C, dtype, dd, 1, sigma, 0))) return rc;
+    return hc.out(dst, dd, bytes);
+}
+
+// ---- conversions and swizzle ----------------------------------------------------
+static int convert_check(int sd, int sc, int dd, int dc, size_t n, size_t *sb, size_t *db) {
+    if (!valid_dtype(sd) || !valid_dtype(dd)) return fail(B200IMG_ERR_BAD_ARG, "convert: bad dtype");
+    if (sc < 1 || sc > 4 || dc < 1 || dc > 4) return fail(B200IMG_ERR_BAD_ARG, "convert: channels must be 1..4");
+    if (!checked_mul(n, (size_t)sc, dtype_size(sd), 1, sb) || !checked_mul(n, (size_t)dc, dtype_size(dd), 1, db))
+        return fail(B200IMG_ERR_DIMENSION, "convert: buffer size overflows");
+    return B200IMG_OK;
+}
+
+int b200img_convert_dev(const void *src, int sd, int sc, void *dst, int dd, int dc, size_t n, int mode,
+                        const float coefs[3], void *stream) {
+    size_t sb, db;
+    int rc = convert_check(sd, sc, dd, dc, n, &sb, &db);
+    if (rc) return rc;
+    return convert_dev(src, sd, sc, dst, dd, dc, n, mode & 1, coefs, (mode & 0x100) ? 1 : 0, (cudaStream_t)stream);
+}
+
+int b200img_convert(const void *src, int sd, int sc, void *dst, int dd, int dc, size_t n, int mode, const float coefs[3]) {
+    size_t sb, db;
+    int rc = convert_check(sd, sc, dd, dc, n, &sb, &db);
+    if (rc) return rc;
+    if (n == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "convert: null buffer");
+    HostCall hc;
+    void *ds, *ddv;
+    if ((rc = hc.in(src, sb, &ds))) return rc;
+    if ((rc = hc.out_buf(db, &ddv))) return rc;
+    if ((rc = convert_dev(ds, sd, sc, ddv, dd, dc, n, mode & 1, coefs, (mode & 0x100) ? 1 : 0, 0))) return rc;
+    return hc.out(dst, ddv, db);
+}
+
+int b200img_swizzle_02_dev(void *buf, int dtype, int channels, size_t nsub, void *stream) {
+    if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "swizzle: bad dtype %d", dtype);
+    return swizzle_dev(buf, dtype, channels, nsub, (cudaStream_t)stream);
+}
+
+int b200img_swizzle_02(void *buf, int dtype, int channels, size_t nsub) {
+    if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "swizzle: bad dtype %d", dtype);
+    if (channels != 3 && channels != 4) return fail(B200IMG_ERR_BAD_ARG, "swizzle: channels must be 3 or 4");
+    size_t bytes;
+    if (!checked_mul(nsub, dtype_size(dtype), 1, 1, &bytes)) return fail(B200IMG_ERR_DIMENSION, "swizzle: buffer size overflows");
+    if (nsub < (size_t)channels) return B200IMG_OK;
+    if (!buf) return fail(B200IMG_ERR_BAD_ARG, "swizzle: null buffer");
+    HostCall hc;
+    void *d;
+    int rc;
+    if ((rc = hc.in(buf, bytes, &d))) return rc;
+    if ((rc = swizzle_dev(d, dtype, channels, nsub, 0))) return rc;
+    return hc.out(buf, d, bytes);
+}
+
+}  // extern "C"

@@ -1,0 +1,367 @@
+// convert.cu -- pixel-format conversions and the BGR(A) swizzle.
+//
+// One persistent, HBM-bound streaming kernel: tiles of 1024 pixels are pulled
+// into shared memory with TMA 1-D bulk copies (cp.async.bulk + mbarrier, two
+// stages in flight), converted pixel-by-pixel out of shared memory, and pushed
+// back with bulk stores.  The staging exists because 3-channel pixels are not
+// 16-byte multiples: through shared memory every global access is a full-line
+// bulk transfer whatever the pixel size.  Unaligned pointers and the ragged
+// last tile take a cooperative element-wise path through the same buffers.
+//
+// Arithmetic follows (bit-exactly):
+//   FromPrimitive                      src/color.rs:540-622
+//   CicpRgb::cast_pixels (mode CAST)   src/metadata/cicp.rs:706-1033, fallback
+//                                      782-887, expand/clamp 620-699, 1064-1108
+//   FromColor (mode CONVERT)           src/color.rs:625-850
+//   RgbToLuma                          src/primitive_sealed.rs:187-231
+//   BgraSwizzle (mode SWIZZLE)         src/primitive_sealed.rs:34-67
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+constexpr int TILE_PX = 1024;
+constexpr int THREADS = 256;
+enum { MODE_CAST = 0, MODE_CONVERT = 1, MODE_SWIZZLE = 2 };
+
+// x / d for integer-valued x, d in {255, 65535}: q = x*r, then one FMA-exact
+// residual correction.  Equal to the IEEE quotient for every u8 / u16 input
+// (checked exhaustively by tests/test_convert.py through the kernel).
+__device__ __forceinline__ float div_exact(float x, float d, float r) {
+    float q = __fmul_rn(x, r);
+    float e = __fmaf_rn(-q, d, x);
+    return __fmaf_rn(e, r, q);
+}
+
+// ---- FromPrimitive, src/color.rs:540-622 ----
+template <typename D, typename S> struct FromPrim;
+template <typename T> struct FromPrim<T, T> { static __device__ __forceinline__ T f(T v) { return v; } };
+template <> struct FromPrim<uint8_t, float> {
+    static __device__ __forceinline__ uint8_t f(float v) {
+        float x = fminf(v, 1.0f);  // NaN -> 1.0
+        return (uint8_t)min(sat_u32_rz(__fadd_rn(__fmul_rn(x, 255.0f), 0.5f)), 255u);
+    }
+};
+template <> struct FromPrim<uint16_t, float> {
+    static __device__ __forceinline__ uint16_t f(float v) {
+        float x = fminf(v, 1.0f);
+        return (uint16_t)min(sat_u32_rz(__fadd_rn(__fmul_rn(x, 65535.0f), 0.5f)), 65535u);
+    }
+};
+template <> struct FromPrim<uint8_t, uint16_t> {
+    static __device__ __forceinline__ uint8_t f(uint16_t c) { return (uint8_t)(((uint32_t)c + 128u) / 257u); }
+};
+template <> struct FromPrim<float, uint16_t> {
+    static __device__ __forceinline__ float f(uint16_t v) { return div_exact((float)v, 65535.0f, 1.0f / 65535.0f); }
+};
+template <> struct FromPrim<float, uint8_t> {
+    static __device__ __forceinline__ float f(uint8_t v) { return div_exact((float)v, 255.0f, 1.0f / 255.0f); }
+};
+template <> struct FromPrim<uint16_t, uint8_t> {
+    static __device__ __forceinline__ uint16_t f(uint8_t c) { return (uint16_t)(((uint32_t)c << 8) | c); }
+};
+
+template <typename T> struct MaxV;
+template <> struct MaxV<uint8_t> { static __device__ __forceinline__ uint8_t v() { return 255; } };
+template <> struct MaxV<uint16_t> { static __device__ __forceinline__ uint16_t v() { return 65535; } };
+template <> struct MaxV<float> { static __device__ __forceinline__ float v() { return 1.0f; } };
+
+// ---- ColorComponentForCicp, src/metadata/cicp.rs:1064-1108 ----
+template <typename T> struct Cicp;
+template <> struct Cicp<uint8_t> {
+    static __device__ __forceinline__ float expand(uint8_t v) { return __fmul_rn((float)v, 1.0f / 255.0f); }
+    static __device__ __forceinline__ uint8_t clamp(float v) { return (uint8_t)min(sat_u32_rz(__fadd_rn(__fmul_rn(v, 255.0f), 0.5f)), 255u); }
+};
+template <> struct Cicp<uint16_t> {
+    static __device__ __forceinline__ float expand(uint16_t v) { return __fmul_rn((float)v, 1.0f / 65535.0f); }
+    static __device__ __forceinline__ uint16_t clamp(float v) { return (uint16_t)min(sat_u32_rz(__fadd_rn(__fmul_rn(v, 65535.0f), 0.5f)), 65535u); }
+};
+template <> struct Cicp<float> {
+    static __device__ __forceinline__ float expand(float v) { return v; }
+    static __device__ __forceinline__ float clamp(float v) { return v; }
+};
+
+// ---- RgbToLuma, src/primitive_sealed.rs:187-231 ----
+__device__ __forceinline__ uint8_t rgb_to_luma(uint8_t r, uint8_t g, uint8_t b) {
+    // ceil(2^24 * {2126, 7152, 722} / 10000)
+    return (uint8_t)(((uint32_t)r * 3566837u + (uint32_t)g * 11999065u + (uint32_t)b * 1211315u + 0x800000u) >> 24);
+}
+__device__ __forceinline__ uint16_t rgb_to_luma(uint16_t r, uint16_t g, uint16_t b) {
+    return (uint16_t)((2126u * (uint32_t)r + 7152u * (uint32_t)g + 722u * (uint32_t)b) / 10000u);
+}
+__device__ __forceinline__ float rgb_to_luma(float r, float g, float b) {
+    const float SR = 2126.0f / 10000.0f, SG = 7152.0f / 10000.0f, SB = 722.0f / 10000.0f;
+    return __fadd_rn(__fadd_rn(__fmul_rn(SR, r), __fmul_rn(SG, g)), __fmul_rn(SB, b));
+}
+
+struct Coefs { float r, g, b; int fused_mac; };
+
+template <int C> struct Layout {
+    static constexpr bool luma = C <= 2;
+    static constexpr bool alpha = (C == 2 || C == 4);
+    static constexpr int colour = C <= 2 ? 1 : 3;
+};
+
+template <typename S, typename D, int CIN, int COUT, int MODE>
+__device__ __forceinline__ void convert_px(const S (&s)[CIN], D (&d)[COUT], const Coefs &k) {
+    using LI = Layout<CIN>;
+    using LO = Layout<COUT>;
+    if constexpr (MODE == MODE_SWIZZLE) {
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) d[c] = (D)s[c == 0 ? 2 : (c == 2 ? 0 : c)];
+    } else if constexpr (LI::luma == LO::luma) {
+        // same family: per-channel FromPrimitive, alpha mapped or DEFAULT_MAX_VALUE
+#pragma unroll
+        for (int c = 0; c < LO::colour; ++c) d[c] = FromPrim<D, S>::f(s[c]);
+        if constexpr (LO::alpha) {
+            if constexpr (LI::alpha) d[LO::colour] = FromPrim<D, S>::f(s[LI::colour]);
+            else d[LO::colour] = MaxV<D>::v();
+        }
+    } else if constexpr (MODE == MODE_CONVERT) {
+        if constexpr (LI::luma) {  // Luma(A) -> Rgb(a): broadcast
+            D g = FromPrim<D, S>::f(s[0]);
+            d[0] = d[1] = d[2] = g;
+            if constexpr (LO::alpha) {
+                if constexpr (LI::alpha) d[3] = FromPrim<D, S>::f(s[1]);
+                else d[3] = MaxV<D>::v();
+            }
+        } else {  // Rgb(a) -> Luma(A): luma in the source type first
+            d[0] = FromPrim<D, S>::f(rgb_to_luma(s[0], s[1], s[2]));
+            if constexpr (LO::alpha) {
+                if constexpr (LI::alpha) d[1] = FromPrim<D, S>::f(s[3]);
+                else d[1] = MaxV<D>::v();
+            }
+        }
+    } else {
+        // cast_pixels_by_fallback: through f32 RGBA
+        float rgba[4];
+        if constexpr (LI::luma) {
+            float l = Cicp<S>::expand(s[0]);
+            rgba[0] = rgba[1] = rgba[2] = l;
+            if constexpr (LI::alpha) rgba[3] = Cicp<S>::expand(s[1]);
+            else rgba[3] = 1.0f;
+        } else {
+            rgba[0] = Cicp<S>::expand(s[0]);
+            rgba[1] = Cicp<S>::expand(s[1]);
+            rgba[2] = Cicp<S>::expand(s[2]);
+            if constexpr (LI::alpha) rgba[3] = Cicp<S>::expand(s[3]);
+            else rgba[3] = 1.0f;
+        }
+        if constexpr (LO::luma) {
+            float luma;
+            if (k.fused_mac) {
+                luma = __fmaf_rn(rgba[0], k.r, 0.0f);
+                luma = __fmaf_rn(rgba[1], k.g, luma);
+                luma = __fmaf_rn(rgba[2], k.b, luma);
+            } else {
+                luma = __fadd_rn(0.0f, __fmul_rn(rgba[0], k.r));
+                luma = __fadd_rn(luma, __fmul_rn(rgba[1], k.g));
+                luma = __fadd_rn(luma, __fmul_rn(rgba[2], k.b));
+            }
+            d[0] = Cicp<D>::clamp(luma);
+            if constexpr (LO::alpha) d[1] = Cicp<D>::clamp(rgba[3]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < COUT; ++c) d[c] = Cicp<D>::clamp(rgba[c]);
+        }
+    }
+}
+
+// pixel <-> shared memory with the widest aligned access the pixel size allows
+template <typename T, int C>
+__device__ __forceinline__ void lds_px(const T *p, T (&v)[C]) {
+    constexpr int B = sizeof(T) * C;
+    if (B == 16) { *reinterpret_cast<uint4 *>(v) = *reinterpret_cast<const uint4 *>(p); }
+    else if (B == 8) { *reinterpret_cast<uint2 *>(v) = *reinterpret_cast<const uint2 *>(p); }
+    else if (B == 4) { *reinterpret_cast<uint32_t *>(v) = *reinterpret_cast<const uint32_t *>(p); }
+    else if (B == 2) { *reinterpret_cast<uint16_t *>(v) = *reinterpret_cast<const uint16_t *>(p); }
+    else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) v[c] = p[c];
+    }
+}
+template <typename T, int C>
+__device__ __forceinline__ void sts_px(T *p, const T (&v)[C]) {
+    constexpr int B = sizeof(T) * C;
+    if (B == 16) { *reinterpret_cast<uint4 *>(p) = *reinterpret_cast<const uint4 *>(v); }
+    else if (B == 8) { *reinterpret_cast<uint2 *>(p) = *reinterpret_cast<const uint2 *>(v); }
+    else if (B == 4) { *reinterpret_cast<uint32_t *>(p) = *reinterpret_cast<const uint32_t *>(v); }
+    else if (B == 2) { *reinterpret_cast<uint16_t *>(p) = *reinterpret_cast<const uint16_t *>(v); }
+    else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) p[c] = v[c];
+    }
+}
+
+template <typename S, typename D, int CIN, int COUT, int MODE>
+__global__ void __launch_bounds__(THREADS)
+convert_kernel(const S *src, D *dst, size_t npixels, Coefs k, int bulk_ok) {
+    constexpr uint32_t IN_BYTES = TILE_PX * CIN * sizeof(S);
+    constexpr uint32_t OUT_BYTES = TILE_PX * COUT * sizeof(D);
+    extern __shared__ __align__(128) unsigned char smem[];
+    S *s_in[2] = {reinterpret_cast<S *>(smem), reinterpret_cast<S *>(smem + IN_BYTES)};
+    D *s_out[2] = {reinterpret_cast<D *>(smem + 2 * IN_BYTES), reinterpret_cast<D *>(smem + 2 * IN_BYTES + OUT_BYTES)};
+    __shared__ uint64_t full[2];
+
+    const size_t n_tiles = (npixels + TILE_PX - 1) / TILE_PX;
+    const size_t n_full = npixels / TILE_PX;  // tiles eligible for bulk copies
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    // bulk prefetch of tile t into stage st (thread 0 only; full tiles only)
+    auto prefetch = [&](size_t t, int st) {
+        if (bulk_ok && t < n_full) {
+            mbar_expect_tx(&full[st], IN_BYTES);
+            bulk_g2s(s_in[st], src + t * (size_t)TILE_PX * CIN, IN_BYTES, &full[st]);
+        }
+    };
+
+    size_t tile = blockIdx.x;
+    if (tid == 0 && tile < n_tiles) prefetch(tile, 0);
+    uint32_t phase[2] = {0, 0};
+    int it = 0;
+    for (; tile < n_tiles; tile += gridDim.x, ++it) {
+        const int st = it & 1;
+        const size_t next = tile + gridDim.x;
+        if (tid == 0 && next < n_tiles) prefetch(next, st ^ 1);  // stage st^1 was released by the barrier ending the previous iteration
+
+        const bool bulk = bulk_ok && tile < n_full;
+        const int px_here = (int)min((size_t)TILE_PX, npixels - tile * TILE_PX);
+        if (bulk) {
+            mbar_wait(&full[st], phase[st]);
+            phase[st] ^= 1;
+        } else {
+            const S *g = src + tile * (size_t)TILE_PX * CIN;
+            for (int i = tid; i < px_here * CIN; i += THREADS) s_in[st][i] = g[i];
+        }
+        // the bulk store that last used s_out[st] (two tiles ago) must have drained
+        if (tid == 0) bulk_wait_read<1>();
+        __syncthreads();
+
+#pragma unroll
+        for (int j = 0; j < TILE_PX / THREADS; ++j) {
+            const int p = tid + j * THREADS;
+            if (p < px_here) {
+                S sv[CIN];
+                D dv[COUT];
+                lds_px<S, CIN>(s_in[st] + p * CIN, sv);
+                convert_px<S, D, CIN, COUT, MODE>(sv, dv, k);
+                sts_px<D, COUT>(s_out[st] + p * COUT, dv);
+            }
+        }
+        if (bulk) fence_async_smem();
+        __syncthreads();
+
+        D *g = dst + tile * (size_t)TILE_PX * COUT;
+        if (bulk) {
+            if (tid == 0) {
+                bulk_s2g(g, s_out[st], OUT_BYTES);
+                bulk_commit();
+            }
+        } else {
+            for (int i = tid; i < px_here * COUT; i += THREADS) g[i] = s_out[st][i];
+        }
+    }
+    if (tid == 0) bulk_wait<0>();
+}
+
+template <typename S, typename D, int CIN, int COUT, int MODE>
+int launch(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStream_t stream) {
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    auto kern = convert_kernel<S, D, CIN, COUT, MODE>;
+    constexpr size_t smem = 2 * (size_t)TILE_PX * (CIN * sizeof(S) + COUT * sizeof(D));
+    static thread_local int blocks_per_sm[64] = {0};
+    int &bps = blocks_per_sm[ctx->device & 63];
+    if (bps == 0) {
+        if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, THREADS, smem));
+        if (bps < 1) bps = 1;
+    }
+    const size_t n_tiles = (npixels + TILE_PX - 1) / TILE_PX;
+    const size_t grid = n_tiles < (size_t)ctx->sm_count * bps ? n_tiles : (size_t)ctx->sm_count * bps;
+    const int bulk_ok = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+    kern<<<(unsigned)grid, THREADS, smem, stream>>>((const S *)src, (D *)dst, npixels, k, bulk_ok);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
+template <typename S, typename D, int CIN, int COUT>
+int launch_mode(const void *src, void *dst, size_t n, int mode, const Coefs &k, cudaStream_t st) {
+    if (Layout<CIN>::luma == Layout<COUT>::luma || mode == B200IMG_CAST)
+        return launch<S, D, CIN, COUT, MODE_CAST>(src, dst, n, k, st);
+    return launch<S, D, CIN, COUT, MODE_CONVERT>(src, dst, n, k, st);
+}
+
+template <typename S, typename D, int CIN>
+int launch_cout(const void *src, void *dst, int cout, size_t n, int mode, const Coefs &k, cudaStream_t st) {
+    switch (cout) {
+        case 1: return launch_mode<S, D, CIN, 1>(src, dst, n, mode, k, st);
+        case 2: return launch_mode<S, D, CIN, 2>(src, dst, n, mode, k, st);
+        case 3: return launch_mode<S, D, CIN, 3>(src, dst, n, mode, k, st);
+        case 4: return launch_mode<S, D, CIN, 4>(src, dst, n, mode, k, st);
+    }
+    return fail(B200IMG_ERR_BAD_ARG, "convert: dst_channels must be 1..4");
+}
+
+template <typename S, typename D>
+int launch_cin(const void *src, int cin, void *dst, int cout, size_t n, int mode, const Coefs &k, cudaStream_t st) {
+    switch (cin) {
+        case 1: return launch_cout<S, D, 1>(src, dst, cout, n, mode, k, st);
+        case 2: return launch_cout<S, D, 2>(src, dst, cout, n, mode, k, st);
+        case 3: return launch_cout<S, D, 3>(src, dst, cout, n, mode, k, st);
+        case 4: return launch_cout<S, D, 4>(src, dst, cout, n, mode, k, st);
+    }
+    return fail(B200IMG_ERR_BAD_ARG, "convert: src_channels must be 1..4");
+}
+
+template <typename S>
+int launch_dst(const void *src, int cin, void *dst, int dd, int cout, size_t n, int mode, const Coefs &k, cudaStream_t st) {
+    switch (dd) {
+        case B200IMG_U8: return launch_cin<S, uint8_t>(src, cin, dst, cout, n, mode, k, st);
+        case B200IMG_U16: return launch_cin<S, uint16_t>(src, cin, dst, cout, n, mode, k, st);
+        case B200IMG_F32: return launch_cin<S, float>(src, cin, dst, cout, n, mode, k, st);
+    }
+    return fail(B200IMG_ERR_BAD_ARG, "convert: bad dst_dtype");
+}
+
+}  // namespace
+
+int convert_dev(const void *src, int sd, int cin, void *dst, int dd, int cout, size_t n, int mode,
+                const float coefs[3], int fused_mac, cudaStream_t st) {
+    if (mode != B200IMG_CAST && mode != B200IMG_CONVERT) return fail(B200IMG_ERR_BAD_ARG, "convert: bad mode %d", mode);
+    if (n == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "convert: null buffer");
+    Coefs k = {0.2126f, 0.7152f, 0.0722f, fused_mac};  // src/images/buffer.rs:1743
+    if (coefs) { k.r = coefs[0]; k.g = coefs[1]; k.b = coefs[2]; }
+    switch (sd) {
+        case B200IMG_U8: return launch_dst<uint8_t>(src, cin, dst, dd, cout, n, mode, k, st);
+        case B200IMG_U16: return launch_dst<uint16_t>(src, cin, dst, dd, cout, n, mode, k, st);
+        case B200IMG_F32: return launch_dst<float>(src, cin, dst, dd, cout, n, mode, k, st);
+    }
+    return fail(B200IMG_ERR_BAD_ARG, "convert: bad src_dtype");
+}
+
+int swizzle_dev(void *buf, int dtype, int channels, size_t nsub, cudaStream_t st) {
+    if (channels != 3 && channels != 4) return fail(B200IMG_ERR_BAD_ARG, "swizzle: channels must be 3 or 4");
+    const size_t n = nsub / (size_t)channels;  // full chunks only (as_chunks_mut)
+    if (n == 0) return B200IMG_OK;
+    if (!buf) return fail(B200IMG_ERR_BAD_ARG, "swizzle: null buffer");
+    Coefs k = {0, 0, 0, 0};
+#define SWZ(T, C) launch<T, T, C, C, MODE_SWIZZLE>(buf, buf, n, k, st)
+    switch (dtype) {
+        case B200IMG_U8: return channels == 3 ? SWZ(uint8_t, 3) : SWZ(uint8_t, 4);
+        case B200IMG_U16: return channels == 3 ? SWZ(uint16_t, 3) : SWZ(uint16_t, 4);
+        case B200IMG_F32: return channels == 3 ? SWZ(float, 3) : SWZ(float, 4);
+    }
+#undef SWZ
+    return fail(B200IMG_ERR_BAD_ARG, "swizzle: bad dtype");
+}
+
+}  // namespace b200

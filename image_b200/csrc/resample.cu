@@ -1,0 +1,507 @@
+// resample.cu -- imageops::resize as ONE fused kernel.
+//
+// The reference runs vertical_sample (src/imageops/sample.rs:494-562) into a
+// full Rgba32F intermediate (16 B per pixel in DRAM) and then horizontal_sample
+// (217-340).  Here a CTA owns a TW x TH tile of the destination: it stages the
+// source rows/columns that tile taps (with their halos) in shared memory, runs
+// the vertical pass into an f32 shared-memory intermediate, runs the horizontal
+// pass out of it, and stores the tile.  The intermediate never touches DRAM, so
+// the kernel's DRAM traffic is the algorithmic minimum (source once through L2,
+// destination once).  The arithmetic order is the reference's: vertical first
+// (accumulator starts at acc_init, taps ascending), then horizontal (starts at
+// 0, taps ascending), then the store rule of src/primitive_sealed.rs:107-147.
+//
+// All reductions run on the FMA pipes; the filter is a banded stencil, not a
+// dense contraction, so tensor cores are not used.
+#include "common.cuh"
+#include "host_tables.h"
+
+#include <list>
+#include <mutex>
+#include <tuple>
+
+namespace b200 {
+namespace {
+
+constexpr int THREADS = 256;
+
+struct ResizeArgs {
+    const void *src;
+    void *dst;
+    size_t src_img_stride, dst_img_stride;  // bytes between images of a batch
+    uint32_t w, C;                          // source width (pixels), channels
+    uint32_t nw;                            // destination width
+    uint32_t src_row0;                      // first source row present in `src` (band mode)
+    uint32_t dst_row0, dst_rows;            // destination rows computed by this launch
+    const int32_t *vleft, *vcount; const float *vw; int vstride;
+    const int32_t *hleft, *hcount; const float *hw; int hstride;
+    float acc_init;
+    int TW, TH;            // tile of the destination
+    int tiles_x, tiles_y;  // per image
+    int max_cols, max_rows;     // bound of the staged source region (pixels, rows)
+    int src_pitch;              // bytes per staged source row
+    int tmp_pitch;              // floats per intermediate row
+};
+
+template <typename T> struct Word;  // 32-bit word of subpixels
+template <> struct Word<uint8_t> {
+    static constexpr int N = 4;
+    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[4]) {
+        f[0] = (float)(w & 0xffu); f[1] = (float)((w >> 8) & 0xffu);
+        f[2] = (float)((w >> 16) & 0xffu); f[3] = (float)(w >> 24);
+    }
+};
+template <> struct Word<uint16_t> {
+    static constexpr int N = 2;
+    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[2]) {
+        f[0] = (float)(w & 0xffffu); f[1] = (float)(w >> 16);
+    }
+};
+template <> struct Word<float> {
+    static constexpr int N = 1;
+    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[1]) { f[0] = __uint_as_float(w); }
+};
+
+// cooperative 2-D copy global -> shared in units of U bytes
+template <typename U>
+__device__ __forceinline__ void stage_rows(const unsigned char *g, size_t g_pitch, unsigned char *s, int s_pitch,
+                                           int rows, int row_bytes, int tid) {
+    const int per_row = row_bytes / (int)sizeof(U);
+    for (int i = tid; i < rows * per_row; i += THREADS) {
+        const int r = i / per_row, v = i - r * per_row;
+        reinterpret_cast<U *>(s + (size_t)r * s_pitch)[v] = __ldg(reinterpret_cast<const U *>(g + (size_t)r * g_pitch) + v);
+    }
+}
+
+template <typename T, int C, bool STRICT>
+__global__ void __launch_bounds__(THREADS)
+resize_kernel(const ResizeArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    // layout: [src region | reused as output staging] [tmp f32] [vw tile] [hw tile (transposed)] [hleft tile]
+    const int src_bytes = a.max_rows * a.src_pitch;
+    unsigned char *s_src = smem;
+    float *s_tmp = reinterpret_cast<float *>(smem + src_bytes);
+    float *s_vw = s_tmp + (size_t)a.TH * a.tmp_pitch;
+    float *s_hw = s_vw + a.TH * a.vstride;
+    int *s_hl = reinterpret_cast<int *>(s_hw + a.TW * a.hstride);
+
+    const int tid = threadIdx.x;
+    const unsigned tiles_per_img = (unsigned)a.tiles_x * a.tiles_y;
+    const unsigned img = blockIdx.x / tiles_per_img;
+    const unsigned trem = blockIdx.x % tiles_per_img;
+    const int ty = trem / a.tiles_x, tx = trem % a.tiles_x;
+
+    const int ox0 = tx * a.TW, oy0 = a.dst_row0 + ty * a.TH;
+    const int tw = min(a.TW, (int)a.nw - ox0);
+    const int th = min(a.TH, (int)(a.dst_row0 + a.dst_rows) - oy0);
+
+    const int col0 = a.hleft[ox0];
+    const int col1 = a.hleft[ox0 + tw - 1] + a.hcount[ox0 + tw - 1];
+    const int row0 = a.vleft[oy0];
+    const int row1 = a.vleft[oy0 + th - 1] + a.vcount[oy0 + th - 1];
+    const int cols = col1 - col0, rows = row1 - row0;
+    const int row_sub = cols * C;  // subpixels per staged row
+
+    const T *src = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(a.src) + (size_t)img * a.src_img_stride);
+    T *dst = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(a.dst) + (size_t)img * a.dst_img_stride);
+
+    // ---- stage weights ----
+    for (int i = tid; i < th * a.vstride; i += THREADS) s_vw[i] = a.vw[(size_t)oy0 * a.vstride + i];
+    for (int i = tid; i < tw * a.hstride; i += THREADS) {
+        const int oxl = i / a.hstride, k = i % a.hstride;
+        s_hw[k * a.TW + oxl] = a.hw[(size_t)(ox0 + oxl) * a.hstride + k];
+    }
+    for (int i = tid; i < tw; i += THREADS) s_hl[i] = a.hleft[ox0 + i] - col0;
+
+    // ---- stage the source region: rows [row0,row1) x cols [col0,col1) ----
+    {
+        const size_t g_pitch = (size_t)a.w * C;  // subpixels
+        const T *g0 = src + (size_t)(row0 - (int)a.src_row0) * g_pitch + (size_t)col0 * C;
+        // widest power-of-two unit that divides the row start, the row pitch and the row length
+        const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(g0) | (sizeof(T) * g_pitch) | (sizeof(T) * row_sub) | 16u);
+        const int unit = (int)(mis & (~mis + 1u));  // lowest set bit: 1, 2, 4, 8 or 16 bytes
+        const unsigned char *gb = reinterpret_cast<const unsigned char *>(g0);
+        const size_t gp = sizeof(T) * g_pitch;
+        const int row_bytes = (int)(sizeof(T) * row_sub);
+        if (unit == 16) stage_rows<uint4>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+        else if (unit == 8) stage_rows<uint2>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+        else if (unit == 4) stage_rows<uint32_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+        else if (unit == 2) stage_rows<uint16_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+        else stage_rows<uint8_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+    }
+    __syncthreads();
+
+    // ---- vertical pass: s_tmp[oyl][s] = acc_init + sum_i src[vleft+i][s] * vw[i] ----
+    {
+        constexpr int N = Word<T>::N;
+        const int words = (row_sub + N - 1) / N;
+        for (int idx = tid; idx < th * words; idx += THREADS) {
+            const int oyl = idx / words, wd = idx % words;
+            const int l = a.vleft[oy0 + oyl] - row0, n = a.vcount[oy0 + oyl];
+            const float *wv = s_vw + oyl * a.vstride;
+            float acc[N];
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[j] = a.acc_init;
+            const unsigned char *p = s_src + (size_t)l * a.src_pitch + wd * 4;
+            for (int i = 0; i < n; ++i) {
+                float f[N];
+                Word<T>::unpack(*reinterpret_cast<const uint32_t *>(p), f);
+                const float wgt = wv[i];
+#pragma unroll
+                for (int j = 0; j < N; ++j) acc[j] = mac<STRICT>(acc[j], f[j], wgt);
+                p += a.src_pitch;
+            }
+            float *t = s_tmp + (size_t)oyl * a.tmp_pitch + wd * N;
+            if (N == 4) *reinterpret_cast<float4 *>(t) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            else if (N == 2) *reinterpret_cast<float2 *>(t) = make_float2(acc[0], acc[1]);
+            else t[0] = acc[0];
+        }
+    }
+    __syncthreads();
+
+    // ---- horizontal pass out of s_tmp; results staged in s_src (now free) ----
+    T *s_out = reinterpret_cast<T *>(s_src);
+    const int out_pitch = a.TW * C;  // subpixels per staged output row
+    {
+        const int items = a.TW * a.TH;  // lane = 8 rows x 4 columns: distinct banks for the float4 reads
+        for (int e = tid; e < items; e += THREADS) {
+            const int oyl = (e / (8 * a.TW)) * 8 + (e & 7);
+            const int oxl = (e >> 3) % a.TW;
+            if (oyl >= th || oxl >= tw) continue;
+            const int n = a.hcount[ox0 + oxl];
+            const float *t = s_tmp + (size_t)oyl * a.tmp_pitch + s_hl[oxl] * C;
+            const float *wh = s_hw + oxl;
+            float acc[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] = 0.0f;
+            for (int i = 0; i < n; ++i) {
+                const float wgt = wh[i * a.TW];
+                float v[C];
+                if (C == 4) { const float4 q = *reinterpret_cast<const float4 *>(t); v[0] = q.x; v[1] = q.y; v[2 % C] = q.z; v[3 % C] = q.w; }
+                else if (C == 2) { const float2 q = *reinterpret_cast<const float2 *>(t); v[0] = q.x; v[1 % C] = q.y; }
+                else {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) v[c] = t[c];
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) acc[c] = mac<STRICT>(acc[c], v[c], wgt);
+                t += C;
+            }
+            T *o = s_out + (size_t)oyl * out_pitch + oxl * C;
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[c] = Px<T>::clamp_nearest(acc[c]);
+        }
+    }
+    __syncthreads();
+
+    // ---- store the tile, row-wise coalesced ----
+    {
+        const size_t d_pitch = (size_t)a.nw * C;
+        T *g0 = dst + (size_t)(oy0 - (int)a.dst_row0) * d_pitch + (size_t)ox0 * C;
+        const int sub = tw * C;
+        const bool vec_ok = (sizeof(T) * d_pitch) % 16 == 0 && (reinterpret_cast<uintptr_t>(g0) & 15) == 0 &&
+                            (sizeof(T) * sub) % 16 == 0 && (sizeof(T) * out_pitch) % 16 == 0;
+        if (vec_ok) {
+            const int v_per_row = (int)(sizeof(T) * sub / 16);
+            for (int i = tid; i < th * v_per_row; i += THREADS) {
+                const int r = i / v_per_row, v = i % v_per_row;
+                reinterpret_cast<uint4 *>(g0 + (size_t)r * d_pitch)[v] =
+                    reinterpret_cast<const uint4 *>(s_out + (size_t)r * out_pitch)[v];
+            }
+        } else {
+            for (int i = tid; i < th * sub; i += THREADS) {
+                const int r = i / sub, s = i % sub;
+                g0[(size_t)r * d_pitch + s] = s_out[(size_t)r * out_pitch + s];
+            }
+        }
+    }
+}
+
+// ---- device-side weight tables, cached per (device, filter, lengths, axis) --------
+struct DevTable {
+    int device, filter, axis;
+    uint32_t src_len, dst_len;
+    AxisTable host;  // left/count kept on the host for tile planning
+    int32_t *d_left = nullptr, *d_count = nullptr;
+    float *d_w = nullptr;
+};
+std::mutex g_tab_mu;
+std::list<DevTable> g_tabs;  // most recently used first
+constexpr size_t MAX_TABLES = 32;
+
+void free_table(DevTable &t) {
+    cudaFree(t.d_left); cudaFree(t.d_count); cudaFree(t.d_w);
+}
+
+int get_table(int device, int filter, uint32_t src_len, uint32_t dst_len, int axis, const DevTable **out) {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    for (auto it = g_tabs.begin(); it != g_tabs.end(); ++it) {
+        if (it->device == device && it->filter == filter && it->axis == axis && it->src_len == src_len && it->dst_len == dst_len) {
+            g_tabs.splice(g_tabs.begin(), g_tabs, it);
+            *out = &g_tabs.front();
+            return B200IMG_OK;
+        }
+    }
+    DevTable t;
+    t.device = device; t.filter = filter; t.axis = axis; t.src_len = src_len; t.dst_len = dst_len;
+    build_axis_table(filter, src_len, dst_len, axis, t.host);
+    const size_t n = dst_len;
+    if (cudaMalloc(&t.d_left, n * 4) != cudaSuccess || cudaMalloc(&t.d_count, n * 4) != cudaSuccess ||
+        cudaMalloc(&t.d_w, t.host.w.size() * 4) != cudaSuccess) {
+        cudaGetLastError();
+        free_table(t);
+        return fail(B200IMG_ERR_OOM, "resize: cannot allocate weight tables");
+    }
+    // synchronous copies: the table is complete before any stream can use it
+    B200_CUDA(cudaMemcpy(t.d_left, t.host.left.data(), n * 4, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(t.d_count, t.host.count.data(), n * 4, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(t.d_w, t.host.w.data(), t.host.w.size() * 4, cudaMemcpyHostToDevice));
+    g_tabs.push_front(std::move(t));
+    if (g_tabs.size() > MAX_TABLES) {
+        // evicting a table a queued kernel still reads would be a use-after-free
+        cudaDeviceSynchronize();
+        free_table(g_tabs.back());
+        g_tabs.pop_back();
+    }
+    *out = &g_tabs.front();
+    return B200IMG_OK;
+}
+
+// Largest staged extent over all tiles of size `tile` along one axis.
+int max_extent(const AxisTable &t, uint32_t first, uint32_t count, int tile) {
+    int m = 1;
+    for (uint32_t o = first; o < first + count; o += tile) {
+        const uint32_t e = std::min<uint32_t>(o + tile, first + count) - 1;
+        m = std::max(m, t.left[e] + t.count[e] - t.left[o]);
+    }
+    return m;
+}
+
+struct Plan { int TW, TH, max_cols, max_rows, src_pitch, tmp_pitch; size_t smem; };
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// Pick the destination tile: smallest staged-source footprint per output pixel
+// that still fits the shared-memory budget and keeps >= 2 CTAs per SM.
+bool plan_tiles(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw,
+                int C, int tsize, size_t smem_budget, Plan *best) {
+    static const int tws[] = {8, 16, 32, 64, 128};
+    static const int ths[] = {8, 16, 32, 64};
+    double best_cost = 1e300;
+    bool found = false;
+    for (int TW : tws) {
+        for (int TH : ths) {
+            if (TW * TH < 256 && !(TW == 8 && TH == 8)) continue;  // keep every thread busy in the horizontal pass
+            Plan p;
+            p.TW = TW; p.TH = TH;
+            p.max_cols = max_extent(ht, 0, nw, TW);
+            p.max_rows = max_extent(vt, dst_row0, dst_rows, TH);
+            const int out_bytes_row = TW * C * tsize;
+            p.src_pitch = round_up(std::max(p.max_cols * C * tsize, out_bytes_row), 16);
+            int tp = round_up(p.max_cols * C, 4);
+            if ((tp / 4) % 2 == 0) tp += 4;  // odd number of 16-byte units: the 8-row lane pattern hits 8 bank groups
+            p.tmp_pitch = tp;
+            const int src_rows_needed = std::max(p.max_rows, (TH * out_bytes_row + p.src_pitch - 1) / p.src_pitch);
+            p.max_rows = src_rows_needed;
+            p.smem = (size_t)p.max_rows * p.src_pitch + (size_t)TH * p.tmp_pitch * 4 + (size_t)TH * vt.stride * 4 +
+                     (size_t)TW * ht.stride * 4 + (size_t)TW * 4;
+            if (p.smem > smem_budget) continue;
+            // cost: staged bytes + intermediate work per destination pixel, with a mild
+            // penalty for tiles so large that few CTAs fit per SM
+            const double staged = (double)p.max_rows * p.max_cols / ((double)TW * TH);
+            const double vwork = (double)p.max_cols / TW;
+            const double occ_pen = p.smem > 100 * 1024 ? 1.3 : (p.smem > 72 * 1024 ? 1.1 : 1.0);
+            const double cost = (staged + 2.0 * vwork) * occ_pen;
+            if (cost < best_cost) { best_cost = cost; *best = p; found = true; }
+        }
+    }
+    return found;
+}
+
+template <typename T, int C>
+int launch_tc(const ResizeArgs &a, size_t smem, unsigned grid, bool strict, cudaStream_t st) {
+    auto k = strict ? resize_kernel<T, C, true> : resize_kernel<T, C, false>;
+    if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, THREADS, smem, st>>>(a);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
+template <typename T>
+int launch_t(const ResizeArgs &a, size_t smem, unsigned grid, bool strict, cudaStream_t st) {
+    switch (a.C) {
+        case 1: return launch_tc<T, 1>(a, smem, grid, strict, st);
+        case 2: return launch_tc<T, 2>(a, smem, grid, strict, st);
+        case 3: return launch_tc<T, 3>(a, smem, grid, strict, st);
+        case 4: return launch_tc<T, 4>(a, smem, grid, strict, st);
+    }
+    return fail(B200IMG_ERR_BAD_ARG, "resize: channels must be 1..4");
+}
+
+// ---- unfused fallback for extreme downscales (the tile's source footprint does not fit
+// shared memory): the reference's own structure, an f32 intermediate in global scratch.
+template <typename T, bool STRICT>
+__global__ void __launch_bounds__(THREADS)
+vertical_kernel(const T *src, float *tmp, size_t row_sub, uint32_t src_row0, uint32_t dst_row0, uint32_t dst_rows,
+                const int32_t *vleft, const int32_t *vcount, const float *vw, int vstride, float acc_init) {
+    const size_t total = (size_t)dst_rows * row_sub;
+    for (size_t idx = (size_t)blockIdx.x * THREADS + threadIdx.x; idx < total; idx += (size_t)gridDim.x * THREADS) {
+        const uint32_t oyl = (uint32_t)(idx / row_sub);
+        const size_t s = idx - (size_t)oyl * row_sub;
+        const uint32_t oy = dst_row0 + oyl;
+        const int l = vleft[oy], n = vcount[oy];
+        const float *w = vw + (size_t)oy * vstride;
+        const T *p = src + (size_t)(l - (int)src_row0) * row_sub + s;
+        float acc = acc_init;
+        for (int i = 0; i < n; ++i) { acc = mac<STRICT>(acc, Px<T>::to_f32(__ldg(p)), w[i]); p += row_sub; }
+        tmp[idx] = acc;
+    }
+}
+
+template <typename T, int C, bool STRICT>
+__global__ void __launch_bounds__(THREADS)
+horizontal_kernel(const float *tmp, T *dst, uint32_t w, uint32_t nw, uint32_t dst_rows,
+                  const int32_t *hleft, const int32_t *hcount, const float *hw, int hstride) {
+    const size_t total = (size_t)dst_rows * nw;
+    for (size_t idx = (size_t)blockIdx.x * THREADS + threadIdx.x; idx < total; idx += (size_t)gridDim.x * THREADS) {
+        const uint32_t oyl = (uint32_t)(idx / nw);
+        const uint32_t ox = (uint32_t)(idx - (size_t)oyl * nw);
+        const int l = hleft[ox], n = hcount[ox];
+        const float *wgt = hw + (size_t)ox * hstride;
+        const float *t = tmp + ((size_t)oyl * w + l) * C;
+        float acc[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[c] = 0.0f;
+        for (int i = 0; i < n; ++i) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) acc[c] = mac<STRICT>(acc[c], t[c], wgt[i]);
+            t += C;
+        }
+        T *o = dst + idx * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) o[c] = Px<T>::clamp_nearest(acc[c]);
+    }
+}
+
+template <typename T, int C>
+int unfused_tc(const void *src, void *dst, float *tmp, const ResizeArgs &a, uint32_t n_images, int sm_count,
+               bool strict, cudaStream_t st) {
+    const size_t row_sub = (size_t)a.w * C;
+    const unsigned grid = (unsigned)std::min<size_t>(((size_t)a.dst_rows * row_sub + THREADS - 1) / THREADS, (size_t)sm_count * 16);
+    const unsigned grid_h = (unsigned)std::min<size_t>(((size_t)a.dst_rows * a.nw + THREADS - 1) / THREADS, (size_t)sm_count * 16);
+    for (uint32_t img = 0; img < n_images; ++img) {
+        const T *s = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(src) + (size_t)img * a.src_img_stride);
+        T *d = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(dst) + (size_t)img * a.dst_img_stride);
+        if (strict) {
+            vertical_kernel<T, true><<<grid, THREADS, 0, st>>>(s, tmp, row_sub, a.src_row0, a.dst_row0, a.dst_rows, a.vleft, a.vcount, a.vw, a.vstride, a.acc_init);
+            horizontal_kernel<T, C, true><<<grid_h, THREADS, 0, st>>>(tmp, d, a.w, a.nw, a.dst_rows, a.hleft, a.hcount, a.hw, a.hstride);
+        } else {
+            vertical_kernel<T, false><<<grid, THREADS, 0, st>>>(s, tmp, row_sub, a.src_row0, a.dst_row0, a.dst_rows, a.vleft, a.vcount, a.vw, a.vstride, a.acc_init);
+            horizontal_kernel<T, C, false><<<grid_h, THREADS, 0, st>>>(tmp, d, a.w, a.nw, a.dst_rows, a.hleft, a.hcount, a.hw, a.hstride);
+        }
+        B200_CUDA(cudaGetLastError());
+    }
+    return B200IMG_OK;
+}
+
+template <typename T>
+int unfused_t(const void *src, void *dst, float *tmp, const ResizeArgs &a, uint32_t n, int sms, bool strict, cudaStream_t st) {
+    switch (a.C) {
+        case 1: return unfused_tc<T, 1>(src, dst, tmp, a, n, sms, strict, st);
+        case 2: return unfused_tc<T, 2>(src, dst, tmp, a, n, sms, strict, st);
+        case 3: return unfused_tc<T, 3>(src, dst, tmp, a, n, sms, strict, st);
+        default: return unfused_tc<T, 4>(src, dst, tmp, a, n, sms, strict, st);
+    }
+}
+
+}  // namespace
+
+int resize_band_src_rows(uint32_t h, uint32_t nh, int filter, uint32_t dst_row0, uint32_t dst_rows,
+                         uint32_t *src_row0, uint32_t *src_rows) {
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize: unknown filter %d", filter);
+    if (h == 0 || nh == 0 || dst_rows == 0 || dst_row0 + (uint64_t)dst_rows > nh)
+        return fail(B200IMG_ERR_BAD_ARG, "resize band: bad row range");
+    AxisTable t;
+    build_axis_table(filter, h, nh, 0, t);
+    const uint32_t e = dst_row0 + dst_rows - 1;
+    *src_row0 = (uint32_t)t.left[dst_row0];
+    *src_rows = (uint32_t)(t.left[e] + t.count[e] - t.left[dst_row0]);
+    return B200IMG_OK;
+}
+
+// Core launcher.  src holds source rows [src_row0, src_row0 + src_rows) of a w x h image (per
+// batch entry); dst receives destination rows [dst_row0, dst_row0 + dst_rows).
+int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h,
+                  int C, int dtype, void *dst, size_t dst_stride, uint32_t dst_row0, uint32_t dst_rows,
+                  uint32_t nw, uint32_t nh, uint32_t n_images, int filter, float acc_init, int flags,
+                  cudaStream_t st) {
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize: unknown filter %d", filter);
+    if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "resize: bad dtype %d", dtype);
+    if (C < 1 || C > 4) return fail(B200IMG_ERR_BAD_ARG, "resize: channels must be 1..4 (the reference is unimplemented beyond 4)");
+    if (n_images == 0 || dst_rows == 0 || nw == 0) return B200IMG_OK;
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    const int tsize = (int)dtype_size(dtype);
+
+    const DevTable *vt, *ht;
+    int rc = get_table(ctx->device, filter, h, nh, 0, &vt);
+    if (rc) return rc;
+    rc = get_table(ctx->device, filter, w, nw, 1, &ht);
+    if (rc) return rc;
+    // copy what we need: a later get_table() may reorder the cache, entries stay valid
+    const uint32_t e = dst_row0 + dst_rows - 1;
+    if ((uint32_t)vt->host.left[dst_row0] < src_row0 ||
+        (uint32_t)(vt->host.left[e] + vt->host.count[e]) > src_row0 + src_rows)
+        return fail(B200IMG_ERR_BAD_ARG, "resize band: source band does not cover the rows the destination band taps");
+
+    ResizeArgs a;
+    a.src = src; a.dst = dst;
+    a.src_img_stride = src_stride ? src_stride : (size_t)w * src_rows * C * tsize;
+    a.dst_img_stride = dst_stride ? dst_stride : (size_t)nw * dst_rows * C * tsize;
+    a.w = w; a.C = (uint32_t)C; a.nw = nw;
+    a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
+    a.vleft = vt->d_left; a.vcount = vt->d_count; a.vw = vt->d_w; a.vstride = vt->host.stride;
+    a.hleft = ht->d_left; a.hcount = ht->d_count; a.hw = ht->d_w; a.hstride = ht->host.stride;
+    a.acc_init = acc_init;
+    const bool strict = (flags & B200IMG_FP_STRICT) != 0;
+
+    Plan p;
+    const size_t budget = std::min<size_t>(ctx->smem_optin, 160 * 1024);
+    const bool fused = !(flags & B200IMG_RESIZE_UNFUSED) &&
+                       plan_tiles(vt->host, ht->host, dst_row0, dst_rows, nw, C, tsize, budget, &p);
+    if (!fused) {
+        size_t tmp_bytes;
+        if (!checked_mul(dst_rows, w, (size_t)C, sizeof(float), &tmp_bytes))
+            return fail(B200IMG_ERR_DIMENSION, "resize: intermediate size overflows");
+        void *tmp;
+        rc = scratch(SCRATCH_A, tmp_bytes, &tmp);
+        if (rc) return rc;
+        switch (dtype) {
+            case B200IMG_U8: return unfused_t<uint8_t>(src, dst, (float *)tmp, a, n_images, ctx->sm_count, strict, st);
+            case B200IMG_U16: return unfused_t<uint16_t>(src, dst, (float *)tmp, a, n_images, ctx->sm_count, strict, st);
+            default: return unfused_t<float>(src, dst, (float *)tmp, a, n_images, ctx->sm_count, strict, st);
+        }
+    }
+
+    a.TW = p.TW; a.TH = p.TH;
+    a.tiles_x = (int)((nw + p.TW - 1) / p.TW);
+    a.tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
+    a.max_cols = p.max_cols; a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.tmp_pitch = p.tmp_pitch;
+    const uint64_t grid = (uint64_t)a.tiles_x * a.tiles_y * n_images;
+    if (grid > 0x7fffffffull) return fail(B200IMG_ERR_DIMENSION, "resize: too many tiles for one launch");
+    switch (dtype) {
+        case B200IMG_U8: return launch_t<uint8_t>(a, p.smem, (unsigned)grid, strict, st);
+        case B200IMG_U16: return launch_t<uint16_t>(a, p.smem, (unsigned)grid, strict, st);
+        default: return launch_t<float>(a, p.smem, (unsigned)grid, strict, st);
+    }
+}
+
+void resize_release_tables(int device) {
+    std::lock_guard<std::mutex> lk(g_tab_mu);
+    for (auto it = g_tabs.begin(); it != g_tabs.end();) {
+        if (it->device == device) { free_table(*it); it = g_tabs.erase(it); }
+        else ++it;
+    }
+}
+
+}  // namespace b200

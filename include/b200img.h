@@ -1,0 +1,213 @@
+/*
+ * b200img.h -- C ABI of libb200img.so: image-rs/image's data-parallel pixel
+ * hot path (resampler, Gaussian / box-approximated blur, pixel-format
+ * conversions, BGR(A) swizzle) as hand-written sm_100a CUDA kernels.
+ *
+ * The reference has no FFI or operator-plugin interface for imageops (its only
+ * plugin API is decoder hooks, src/hooks.rs:77-152), so the drop-in boundary
+ * is this library: plain pointers and sizes, no torch / C++ types.  Each entry
+ * point cites the reference function it replaces (file:line relative to the
+ * image-rs/image repository).  INTEGRATION.md shows the Rust `extern "C"`
+ * block a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - Images are packed row-major, interleaved channels, no row padding -- the
+ *     packed case of the reference's #[repr(C)] SampleLayout
+ *     (src/images/flat.rs:97-118; src/images/buffer.rs:550-557).
+ *   - dtype: B200IMG_U8 / U16 / F32 subpixels; channels 1..4 = Luma, LumaA,
+ *     Rgb, Rgba.
+ *   - Every function returns 0 on success or a negative b200img_status and
+ *     never unwinds; b200img_last_error() gives the thread's last message.
+ *     Where the reference panics (asserts in sample.rs:1134-1158, 1211-1214,
+ *     `unimplemented!` for > 4 channels) the call returns B200IMG_ERR_BAD_ARG;
+ *     where it returns ImageError::Limits(DimensionError)
+ *     (src/imageops/filter_1d.rs:638-647) it returns B200IMG_ERR_DIMENSION.
+ *   - `*_dev` entry points take DEVICE pointers valid on the current CUDA
+ *     device and enqueue on `stream` (a cudaStream_t passed as void*, NULL =
+ *     the legacy default stream) without synchronising.  The entry points
+ *     without the suffix take HOST pointers, copy in, run, copy out, and
+ *     return after the result is in `dst`.
+ *   - There is no CPU fallback: without a usable GPU every compute entry point
+ *     fails with B200IMG_ERR_CUDA.
+ *   - Thread-safe.  Scratch memory and weight tables are cached per device.
+ */
+#ifndef B200IMG_H
+#define B200IMG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    B200IMG_OK = 0,
+    B200IMG_ERR_BAD_ARG = -1,     /* the reference would panic / not compile */
+    B200IMG_ERR_DIMENSION = -2,   /* ImageError::Limits(DimensionError) */
+    B200IMG_ERR_OOM = -3,         /* device or pinned-host allocation failed */
+    B200IMG_ERR_CUDA = -4,        /* no device, launch failure, ... */
+    B200IMG_ERR_UNSUPPORTED = -5
+} b200img_status;
+
+typedef enum { B200IMG_U8 = 0, B200IMG_U16 = 1, B200IMG_F32 = 2 } b200img_dtype;
+
+/* FilterType, src/imageops/sample.rs:98-115 */
+typedef enum {
+    B200IMG_NEAREST = 0, B200IMG_TRIANGLE = 1, B200IMG_CATMULLROM = 2,
+    B200IMG_GAUSSIAN = 3, B200IMG_LANCZOS3 = 4
+} b200img_filter;
+
+/* Arithmetic flags.  FAST lets f32 multiply-adds fuse (FFMA); results of the
+ * f32-accumulating filters are then within +-1 LSB (u8/u16) or 1e-5 relative
+ * (f32) of the reference.  STRICT keeps every multiply and add separately
+ * rounded, in the reference's order: bit-exact with a default x86-64 build of
+ * the reference given the same libm.  Integer paths (conversions, swizzle,
+ * Nearest, u8 box blur, Q0.15 Gaussian) are bit-exact under either flag. */
+#define B200IMG_FP_FAST 0
+#define B200IMG_FP_STRICT 1
+/* multiply_accumulate of the reference fuses when it is built with +fma or for
+ * aarch64 (src/math/utils.rs:7-47).  With STRICT, add this bit to reproduce
+ * such a build in the Gaussian engine and the Luma<->RGB fallback. */
+#define B200IMG_FP_FUSED_MAC 2
+/* Resampler only: run the reference's own structure (vertical kernel, f32
+ * intermediate in device scratch, horizontal kernel) instead of the fused
+ * tile kernel.  Chosen automatically when a downscale is so extreme that a
+ * tile's source footprint does not fit shared memory. */
+#define B200IMG_RESIZE_UNFUSED 256
+
+const char *b200img_last_error(void);
+int b200img_version(void);
+int b200img_device_count(int *count);
+
+/* Pinned host memory for the host-pointer entry points (optional; any host
+ * pointer works, pinned ones copy at full PCIe rate). */
+int b200img_pinned_alloc(size_t bytes, void **out);
+int b200img_pinned_free(void *p);
+/* Drop this thread's current device's cached scratch / tables. */
+int b200img_release_caches(void);
+
+/* ---- host-side tables (what the reference computes per call on the CPU) -- */
+
+/* Filter{kernel,support} table in resize(), src/imageops/sample.rs:993-1014;
+ * kernel functions 127-205. */
+float b200img_filter_support(int filter);
+float b200img_filter_kernel(int filter, float x);
+/* `max_ks`, src/imageops/sample.rs:242. */
+int b200img_resize_max_taps(int filter, uint32_t src_len, uint32_t dst_len);
+/* Weight generation of vertical_sample (axis 0, f32 centre;
+ * src/imageops/sample.rs:514-544) and horizontal_sample (axis 1, f64 centre;
+ * 237-307).  left/count have dst_len entries; weights is dst_len x stride,
+ * zero-padded, normalised by division exactly as the reference does. */
+int b200img_build_weights(int filter, uint32_t src_len, uint32_t dst_len, int axis,
+                          int32_t *left, int32_t *count, float *weights, int stride);
+/* resize_dimensions, src/math/utils.rs:56-84 (DynamicImage::resize /
+ * resize_to_fill / thumbnail call it before resizing). */
+int b200img_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill,
+                              uint32_t *out_w, uint32_t *out_h);
+
+/* GaussianBlurParameters, src/imageops/sample.rs:1081-1295 */
+typedef struct {
+    uint32_t x_kernel_size; float x_sigma;
+    uint32_t y_kernel_size; float y_sigma;
+} b200img_gauss_params;
+int b200img_gauss_params_from_radius(float radius, b200img_gauss_params *out);       /* 1132-1142 */
+int b200img_gauss_params_from_kernel_size(float ks, b200img_gauss_params *out);      /* 1148-1166 */
+int b200img_gauss_params_from_anisotropic(float xks, float yks, b200img_gauss_params *out); /* 1172-1204 */
+int b200img_gauss_params_from_sigma(float sigma, b200img_gauss_params *out);         /* 1210-1249 */
+/* get_gaussian_kernel_1d, src/imageops/sample.rs:1057-1077 */
+int b200img_gaussian_kernel_1d(uint32_t width, float sigma, float *out);
+/* boxes_for_gauss(sigma, 3), src/imageops/fast_blur.rs:201-226 */
+int b200img_boxes_for_gauss(float sigma, uint32_t out_radii[3]);
+
+/* ---- resampler ----------------------------------------------------------
+ * imageops::resize, src/imageops/sample.rs:970-1019 (vertical_sample 494-562
+ * then horizontal_sample 217-340, store rule src/primitive_sealed.rs:107-147).
+ * acc_init is the vertical accumulator's start value: 1.0f reproduces the
+ * reference literally (`Rgba([1.0; 4])`, sample.rs:547), 0.0f is the
+ * mathematically intended filter.  An empty source gives a zero-filled
+ * destination (977-984); equal dimensions give a copy (987-991). */
+int b200img_resize(const void *src, uint32_t w, uint32_t h, int channels, int dtype,
+                   void *dst, uint32_t nw, uint32_t nh, int filter, float acc_init, int flags);
+int b200img_resize_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                       void *d_dst, uint32_t nw, uint32_t nh, int filter, float acc_init,
+                       int flags, void *stream);
+/* Device-resident batch variant: n_images equally-shaped images,
+ * src_stride / dst_stride bytes apart (0 = tightly packed).  One launch. */
+int b200img_resize_batch_dev(const void *d_src, size_t src_stride, uint32_t w, uint32_t h,
+                             int channels, int dtype, void *d_dst, size_t dst_stride,
+                             uint32_t nw, uint32_t nh, uint32_t n_images, int filter,
+                             float acc_init, int flags, void *stream);
+/* One row band of a larger resize (multi-GPU single-image split): computes
+ * destination rows [dst_row0, dst_row0 + dst_rows) of the nw x nh result.
+ * d_src_band holds source rows [src_row0, src_row0 + src_rows) of the w x h
+ * source, which must cover every row those destination rows tap (query with
+ * b200img_resize_band_src_rows).  d_dst_band receives dst_rows x nw pixels. */
+int b200img_resize_band_src_rows(uint32_t h, uint32_t nh, int filter, uint32_t dst_row0,
+                                 uint32_t dst_rows, uint32_t *src_row0, uint32_t *src_rows);
+int b200img_resize_band_dev(const void *d_src_band, uint32_t src_row0, uint32_t src_rows,
+                            uint32_t w, uint32_t h, int channels, int dtype, void *d_dst_band,
+                            uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh,
+                            int filter, float acc_init, int flags, void *stream);
+
+/* ---- Gaussian blur -------------------------------------------------------
+ * path GENERIC = imageops::blur / blur_advanced (src/imageops/sample.rs:
+ * 1034-1055, gaussian_blur_indirect 1492-1604): f32 engine for every dtype,
+ * one rounding at the end.  path DYN = DynamicImage::blur / blur_advanced
+ * (src/images/dynimage.rs:1226-1245, gaussian_blur_dyn_image sample.rs:
+ * 1297-1490): Q0.15 fixed point with a u32 accumulator for u8 and u16
+ * (bit-exact), f32 engine for f32.  Engine: filter_2d_separable,
+ * src/imageops/filter_1d.rs:615-761 (row 323-390, column 171-316, clamp-to-
+ * edge 60-130, store 132-164, Q15 transform 392-420, zero-end strip 423-437). */
+#define B200IMG_BLUR_GENERIC 0
+#define B200IMG_BLUR_DYN 1
+int b200img_gaussian_blur(const void *src, uint32_t w, uint32_t h, int channels, int dtype,
+                          void *dst, const b200img_gauss_params *params, int path, int flags);
+int b200img_gaussian_blur_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                              void *d_dst, const b200img_gauss_params *params, int path,
+                              int flags, void *stream);
+int b200img_gaussian_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int channels,
+                                    int dtype, void *d_dst, uint32_t n_images,
+                                    const b200img_gauss_params *params, int path, int flags,
+                                    void *stream);
+
+/* ---- box-approximated blur ----------------------------------------------
+ * imageops::fast_blur / DynamicImage::fast_blur, src/imageops/fast_blur.rs:
+ * 111-191 (horizontal pass 303-413, vertical pass 416-473, accumulators
+ * 36-94).  u8: exact integer; u16: exact while kernel*65535 < 2^24. */
+int b200img_fast_blur(const void *src, uint32_t w, uint32_t h, int channels, int dtype,
+                      void *dst, float sigma);
+int b200img_fast_blur_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                          void *d_dst, float sigma, void *stream);
+int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int channels,
+                                int dtype, void *d_dst, uint32_t n_images, float sigma,
+                                void *stream);
+
+/* ---- pixel-format conversions --------------------------------------------
+ * mode CAST    = DynamicImage::to_* / into_* (src/images/dynimage.rs:320-568
+ *                -> CicpRgb::cast_pixels src/metadata/cicp.rs:706-1033;
+ *                Luma<->RGB through the f32 fallback 782-887 with `coefs`,
+ *                NULL = [0.2126, 0.7152, 0.0722], src/images/buffer.rs:1743).
+ * mode CONVERT = ImageBuffer::convert (src/images/buffer.rs:1643-1654 ->
+ *                FromColor src/color.rs:625-850, integer sRGB luma
+ *                src/primitive_sealed.rs:187-231).
+ * Per-channel rule: FromPrimitive, src/color.rs:540-622.  Bit-exact. */
+#define B200IMG_CAST 0
+#define B200IMG_CONVERT 1
+int b200img_convert(const void *src, int src_dtype, int src_channels, void *dst, int dst_dtype,
+                    int dst_channels, size_t npixels, int mode, const float coefs[3]);
+int b200img_convert_dev(const void *d_src, int src_dtype, int src_channels, void *d_dst,
+                        int dst_dtype, int dst_channels, size_t npixels, int mode,
+                        const float coefs[3], void *stream);
+
+/* BgraSwizzle, src/primitive_sealed.rs:34-67; callers ImageBuffer::
+ * {from_raw_bgr, into_raw_bgr, from_raw_bgra, into_raw_bgra},
+ * src/images/buffer.rs:1544-1582.  In place; swaps subpixel 0 and 2 of every
+ * full 3- or 4-subpixel chunk; a trailing partial chunk is left untouched. */
+int b200img_swizzle_02(void *buf, int dtype, int channels, size_t nsubpixels);
+int b200img_swizzle_02_dev(void *d_buf, int dtype, int channels, size_t nsubpixels, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200IMG_H */

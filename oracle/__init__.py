@@ -1,0 +1,238 @@
+"""CPU oracle for the image-rs pixel hot path -- TEST INFRASTRUCTURE ONLY.
+
+ctypes bindings over ``oracle/_build/liboracle.so`` (C++ restatement of the
+reference's Rust, see ``oracle.h`` for citations).  Only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline legs may import
+this package; ``image_b200`` never does.
+
+Images are numpy arrays of shape (h, w, c) (or (h, w) for one channel) and
+dtype uint8 / uint16 / float32, C-contiguous.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "liboracle.so")
+
+NEAREST, TRIANGLE, CATMULLROM, GAUSSIAN, LANCZOS3 = range(5)
+FILTERS = {"nearest": NEAREST, "triangle": TRIANGLE, "catmullrom": CATMULLROM,
+           "gaussian": GAUSSIAN, "lanczos3": LANCZOS3}
+CAST, CONVERT = 0, 1
+_DT = {np.dtype(np.uint8): 0, np.dtype(np.uint16): 1, np.dtype(np.float32): 2}
+_NP = {0: np.uint8, 1: np.uint16, 2: np.float32}
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with its Makefile (gcc only; no GPU, no reference sources)."""
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".h")) or f == "Makefile"]
+    stale = (not os.path.exists(_SO)) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", _HERE] + (["-B"] if force else []),
+                              stdout=subprocess.DEVNULL)
+    return _SO
+
+
+class GaussParams(C.Structure):
+    _fields_ = [("x_kernel_size", C.c_uint32), ("x_sigma", C.c_float),
+                ("y_kernel_size", C.c_uint32), ("y_sigma", C.c_float)]
+
+    def __repr__(self):
+        return (f"GaussParams(x=({self.x_kernel_size}, {self.x_sigma}), "
+                f"y=({self.y_kernel_size}, {self.y_sigma}))")
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_SO)
+        vp, u32, i, f, sz = C.c_void_p, C.c_uint32, C.c_int, C.c_float, C.c_size_t
+        L.orc_set_fused_mac.argtypes = [i]
+        L.orc_filter_support.argtypes = [i]; L.orc_filter_support.restype = f
+        L.orc_filter_kernel.argtypes = [i, f]; L.orc_filter_kernel.restype = f
+        L.orc_resize_max_taps.argtypes = [i, u32, u32]
+        L.orc_resize_weights.argtypes = [i, u32, u32, i, vp, vp, vp, i]
+        L.orc_resize.argtypes = [vp, u32, u32, i, i, vp, u32, u32, i, f]
+        L.orc_resize_mt.argtypes = [vp, u32, u32, i, i, vp, u32, u32, i, f, i]
+        P = C.POINTER(GaussParams)
+        L.orc_gauss_params_from_radius.argtypes = [f, P]
+        L.orc_gauss_params_from_kernel_size.argtypes = [f, P]
+        L.orc_gauss_params_from_anisotropic.argtypes = [f, f, P]
+        L.orc_gauss_params_from_sigma.argtypes = [f, P]
+        L.orc_gaussian_kernel_1d.argtypes = [u32, f, vp]; L.orc_gaussian_kernel_1d.restype = None
+        L.orc_gaussian_blur_generic.argtypes = [vp, u32, u32, i, i, vp, P]
+        L.orc_gaussian_blur_dyn.argtypes = [vp, u32, u32, i, i, vp, P]
+        L.orc_q15_kernel.argtypes = [vp, i, vp]
+        L.orc_boxes_for_gauss.argtypes = [f, vp]; L.orc_boxes_for_gauss.restype = None
+        L.orc_fast_blur.argtypes = [vp, u32, u32, i, i, vp, f]
+        L.orc_u8_box_store.argtypes = [u32, u32]; L.orc_u8_box_store.restype = C.c_uint8
+        L.orc_convert.argtypes = [vp, i, i, vp, i, i, sz, i, vp]
+        L.orc_swizzle_02.argtypes = [vp, i, i, sz]
+        pu32 = C.POINTER(u32)
+        L.orc_resize_dimensions.argtypes = [u32, u32, u32, u32, i, pu32, pu32]
+        L.orc_resize_dimensions.restype = None
+        _lib = L
+    return _lib
+
+
+def _img(a):
+    a = np.ascontiguousarray(a)
+    if a.dtype not in _DT:
+        raise TypeError(f"unsupported dtype {a.dtype}")
+    if a.ndim == 2:
+        a = a[:, :, None]
+    if a.ndim != 3 or not 1 <= a.shape[2] <= 4:
+        raise ValueError(f"expected (h, w, c<=4), got {a.shape}")
+    return a
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _filter(f):
+    return FILTERS[f.lower()] if isinstance(f, str) else int(f)
+
+
+def set_fused_mac(fused: bool):
+    lib().orc_set_fused_mac(int(bool(fused)))
+
+
+def filter_support(f) -> float:
+    return lib().orc_filter_support(_filter(f))
+
+
+def filter_kernel(f, x: float) -> float:
+    return lib().orc_filter_kernel(_filter(f), float(x))
+
+
+def resize_weights(f, src_len: int, dst_len: int, axis: int):
+    """(left[int32], count[int32], weights[dst_len, max_taps] f32); axis 0 = vertical rule, 1 = horizontal."""
+    L = lib()
+    mt = max(L.orc_resize_max_taps(_filter(f), src_len, dst_len), 1)
+    left = np.zeros(dst_len, np.int32)
+    cnt = np.zeros(dst_len, np.int32)
+    w = np.zeros((dst_len, mt), np.float32)
+    rc = L.orc_resize_weights(_filter(f), src_len, dst_len, axis, _ptr(left), _ptr(cnt), _ptr(w), mt)
+    if rc:
+        raise RuntimeError(f"orc_resize_weights rc={rc}")
+    return left, cnt, w
+
+
+def resize(img, nw: int, nh: int, f, acc_init: float = 1.0, threads: int = 1):
+    """imageops::resize (src/imageops/sample.rs:970).  acc_init=1.0 is the literal reference."""
+    a = _img(img)
+    h, w, c = a.shape
+    out = np.zeros((nh, nw, c), a.dtype)
+    rc = lib().orc_resize_mt(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), nw, nh, _filter(f),
+                             float(acc_init), int(threads))
+    if rc:
+        raise RuntimeError(f"orc_resize rc={rc}")
+    return out
+
+
+def _params(fn, *args) -> GaussParams:
+    p = GaussParams()
+    if fn(*args, C.byref(p)):
+        raise ValueError("invalid Gaussian blur parameter (the reference panics here)")
+    return p
+
+
+def gauss_params_from_radius(r):
+    return _params(lib().orc_gauss_params_from_radius, float(r))
+
+
+def gauss_params_from_kernel_size(k):
+    return _params(lib().orc_gauss_params_from_kernel_size, float(k))
+
+
+def gauss_params_from_anisotropic(xk, yk):
+    return _params(lib().orc_gauss_params_from_anisotropic, float(xk), float(yk))
+
+
+def gauss_params_from_sigma(s):
+    return _params(lib().orc_gauss_params_from_sigma, float(s))
+
+
+def gaussian_kernel_1d(width: int, sigma: float):
+    out = np.zeros(width, np.float32)
+    lib().orc_gaussian_kernel_1d(width, float(sigma), _ptr(out))
+    return out
+
+
+def q15_kernel(k):
+    k = np.ascontiguousarray(k, np.float32)
+    out = np.zeros(len(k), np.uint32)
+    n = lib().orc_q15_kernel(_ptr(k), len(k), _ptr(out))
+    return out[:n]
+
+
+def gaussian_blur(img, params: GaussParams, path: str = "generic"):
+    """path 'generic' = imageops::blur/blur_advanced (f32 engine);
+    'dyn' = DynamicImage::blur/blur_advanced (Q0.15 for u8/u16)."""
+    a = _img(img)
+    h, w, c = a.shape
+    out = np.zeros_like(a)
+    fn = lib().orc_gaussian_blur_generic if path == "generic" else lib().orc_gaussian_blur_dyn
+    rc = fn(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), C.byref(params))
+    if rc:
+        raise RuntimeError(f"gaussian blur rc={rc}")
+    return out
+
+
+def boxes_for_gauss(sigma: float):
+    out = (C.c_size_t * 3)()
+    lib().orc_boxes_for_gauss(float(sigma), out)
+    return list(out)
+
+
+def fast_blur(img, sigma: float):
+    a = _img(img)
+    h, w, c = a.shape
+    out = a.copy()
+    rc = lib().orc_fast_blur(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), float(sigma))
+    if rc:
+        raise RuntimeError(f"orc_fast_blur rc={rc}")
+    return out
+
+
+def u8_box_store(acc: int, ks: int) -> int:
+    return lib().orc_u8_box_store(acc, ks)
+
+
+def convert(pixels, src_channels: int, dst_dtype, dst_channels: int, mode: int = CAST, coefs=None):
+    """pixels: flat or (n, src_channels) array.  Returns (n, dst_channels)."""
+    a = np.ascontiguousarray(pixels).reshape(-1, src_channels)
+    n = a.shape[0]
+    out = np.zeros((n, dst_channels), np.dtype(dst_dtype))
+    cf = None
+    if coefs is not None:
+        cf = np.ascontiguousarray(coefs, np.float32)
+    rc = lib().orc_convert(_ptr(a), _DT[a.dtype], src_channels, _ptr(out), _DT[out.dtype],
+                           dst_channels, n, mode, _ptr(cf) if cf is not None else None)
+    if rc:
+        raise RuntimeError(f"orc_convert rc={rc}")
+    return out
+
+
+def swizzle_02(buf, channels: int):
+    """In place on a copy: returns the swizzled flat array (trailing partial chunk untouched)."""
+    a = np.ascontiguousarray(buf).copy().reshape(-1)
+    rc = lib().orc_swizzle_02(_ptr(a), _DT[a.dtype], channels, a.size)
+    if rc:
+        raise RuntimeError(f"orc_swizzle_02 rc={rc}")
+    return a
+
+
+def resize_dimensions(w, h, nw, nh, fill: bool):
+    ow, oh = C.c_uint32(), C.c_uint32()
+    lib().orc_resize_dimensions(w, h, nw, nh, int(fill), C.byref(ow), C.byref(oh))
+    return ow.value, oh.value
