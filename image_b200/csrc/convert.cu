@@ -280,7 +280,7 @@ int launch(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStrea
     static thread_local int blocks_per_sm[64] = {0};
     int &bps = blocks_per_sm[ctx->device & 63];
     if (bps == 0) {
-        if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, THREADS, smem));
         if (bps < 1) bps = 1;
     }

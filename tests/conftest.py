@@ -70,3 +70,19 @@ def rand_image(rng, h, w, c, dtype):
     if dtype == np.float32:
         return rng.random((h, w, c), dtype=np.float32)
     return rng.integers(0, np.iinfo(dtype).max + 1, (h, w, c), dtype=dtype)
+
+
+def same(got, want):
+    """Bit-identical, except that any NaN matches any NaN: an x86 host produces the 'default NaN'
+    0xFFC00000 where the GPU produces 0x7FFFFFFF; which NaN comes out is not part of the
+    reference's contract (and differs between the CPU targets it supports)."""
+    got, want = np.asarray(got), np.asarray(want)
+    if got.shape != want.shape or got.dtype != want.dtype:
+        return False
+    if got.dtype.kind != "f":
+        return got.tobytes() == want.tobytes()
+    nan = np.isnan(want)
+    if not np.array_equal(np.isnan(got), nan):
+        return False
+    gi, wi = got.view(np.uint32), want.view(np.uint32)
+    return bool(np.array_equal(gi[~nan], wi[~nan]))

@@ -1,0 +1,131 @@
+"""GPU parity: Gaussian blur (f32 engine and Q0.15 engine) and fast_blur against the oracle."""
+import numpy as np
+import pytest
+
+import oracle as o
+from conftest import bench_image, rand_image
+from image_b200 import DynamicImage, GaussianBlurParameters, ImageBuffer, imageops
+from image_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+DT = [np.uint8, np.uint16, np.float32]
+
+
+def _oparams(p):
+    r = p.raw
+    q = o.GaussParams(r.x_kernel_size, r.x_sigma, r.y_kernel_size, r.y_sigma)
+    return q
+
+
+def _gauss_check(img, p, cuda, host=False):
+    import torch
+    src = img if host else torch.from_numpy(img).to(cuda)
+    get = (lambda t: t) if host else (lambda t: t.cpu().numpy())
+    # DynamicImage path: Q0.15 integer for u8/u16 -> bit-exact under either flag
+    want_dyn = o.gaussian_blur(img, _oparams(p), "dyn")
+    flags_dyn = L.FP_FAST if img.dtype != np.float32 else L.FP_STRICT
+    got = get(imageops.blur_dyn(src, p, flags=flags_dyn))
+    assert got.tobytes() == want_dyn.tobytes(), f"dyn path differs {img.dtype} {img.shape} {p}"
+    # generic path: f32 engine; STRICT bit-exact, FAST within tolerance
+    want = o.gaussian_blur(img, _oparams(p), "generic")
+    got = get(imageops.blur_advanced(src, p, flags=L.FP_STRICT))
+    assert got.tobytes() == want.tobytes(), f"generic strict differs {img.dtype} {img.shape} {p}"
+    fast = get(imageops.blur_advanced(src, p))
+    if img.dtype == np.float32:
+        assert np.allclose(fast, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.abs(fast.astype(np.int64) - want.astype(np.int64)).max() <= 1
+
+
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_gaussian_all_types(cuda, dtype, c):
+    rng = np.random.default_rng(20 + c)
+    img = rand_image(rng, 45, 67, c, dtype)
+    for p in (GaussianBlurParameters.new_from_sigma(1.3), GaussianBlurParameters.new_from_radius(4.0),
+              GaussianBlurParameters.SMOOTHING_3, GaussianBlurParameters.new_anisotropic_kernel_size(9.0, 3.0)):
+        _gauss_check(img, p, cuda)
+
+
+def test_gaussian_k2_kernels_reduced(cuda):
+    """BASELINE config 2 kernels (21 taps = blur(img, 10.0); 65 taps = sigma 10) on a 4K crop."""
+    img = bench_image(3840, 2160, 3)[500:900, 1000:1700].copy()
+    for p in (GaussianBlurParameters.new_from_radius(10.0), GaussianBlurParameters.new_from_sigma(10.0)):
+        _gauss_check(img, p, cuda)
+
+
+def test_gaussian_kernel_wider_than_image_and_fused_mac(cuda):
+    import torch
+    rng = np.random.default_rng(31)
+    img = rand_image(rng, 5, 9, 3, np.uint8)
+    _gauss_check(img, GaussianBlurParameters.new_from_sigma(10.0), cuda)   # 65 taps over a 9x5 image
+    _gauss_check(img, GaussianBlurParameters.new_from_sigma(9.0), cuda, host=True)  # >= 55 taps: transient variant
+    # multiply_accumulate fused (aarch64 / +fma builds of the reference)
+    f = rand_image(rng, 33, 35, 3, np.float32)
+    p = GaussianBlurParameters.new_from_sigma(2.0)
+    o.set_fused_mac(True)
+    try:
+        want = o.gaussian_blur(f, _oparams(p), "generic")
+    finally:
+        o.set_fused_mac(False)
+    got = imageops.blur_advanced(torch.from_numpy(f).to(cuda), p, flags=L.FP_STRICT | L.FP_FUSED_MAC).cpu().numpy()
+    assert got.tobytes() == want.tobytes()
+
+
+def test_gaussian_one_tap_quirks(cuda):
+    """blur(img, 0.0) (src/imageops/mod.rs:473-478): 1-tap kernels shift right and leave row 0 zero."""
+    rng = np.random.default_rng(32)
+    for dtype in DT:
+        img = rand_image(rng, 7, 8, 2, dtype)
+        _gauss_check(img, GaussianBlurParameters.new_from_radius(0.0), cuda)
+        _gauss_check(img, GaussianBlurParameters.new_from_sigma(0.05), cuda)
+        _gauss_check(img, GaussianBlurParameters.new_anisotropic_kernel_size(1.0, 5.0), cuda)
+        _gauss_check(img, GaussianBlurParameters.new_anisotropic_kernel_size(5.0, 1.0), cuda)
+
+
+def test_gaussian_constant_and_dynimage(cuda):
+    img = np.full((40, 50, 4), 201, np.uint8)
+    d = DynamicImage(ImageBuffer(img))
+    assert (d.blur(3.0).buf.data == 201).all()
+    assert (d.blur_advanced(GaussianBlurParameters.new_from_sigma(5.0)).buf.data == 201).all()
+    assert (imageops.blur(img, 3.0) == 201).all()
+
+
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_fast_blur_all_types(cuda, dtype, c):
+    import torch
+    rng = np.random.default_rng(40 + c)
+    img = rand_image(rng, 53, 71, c, dtype)
+    for sigma in (0.0, 0.7, 3.0, 10.0):
+        want = o.fast_blur(img, sigma)
+        got = imageops.fast_blur(torch.from_numpy(img).to(cuda), sigma).cpu().numpy()
+        if dtype == np.float32:
+            assert np.allclose(got, want, rtol=1e-5, atol=2e-6), sigma
+        else:
+            assert got.tobytes() == want.tobytes(), (dtype, c, sigma)
+
+
+def test_fast_blur_k2_reduced_and_host(cuda):
+    img = bench_image(3840, 2160, 3)[300:800, 200:1100].copy()
+    assert np.array_equal(imageops.fast_blur(img, 10.0), o.fast_blur(img, 10.0))
+
+
+def test_fast_blur_large_sigma_and_tiny_images(cuda):
+    rng = np.random.default_rng(41)
+    for shape in ((1, 1, 3), (1, 17, 1), (23, 1, 4), (6, 5, 2)):
+        img = rand_image(rng, *shape, np.uint8)
+        for sigma in (1.0, 50.0, 300.0):
+            assert np.array_equal(imageops.fast_blur(img, sigma), o.fast_blur(img, sigma)), (shape, sigma)
+    assert imageops.fast_blur(np.zeros((0, 0, 3), np.uint8), 3.0).size == 0
+    assert np.array_equal(imageops.fast_blur(rand_image(rng, 9, 9, 3, np.uint8), -3.0).shape, (9, 9, 3))
+
+
+def test_fast_blur_constant_image_property_4k(cuda):
+    """fast_blur.rs:535-592 at the K2 size: a constant image stays constant."""
+    import torch
+    img = torch.full((2160, 3840, 3), 143, dtype=torch.uint8, device=cuda)
+    out = imageops.fast_blur(img, 10.0)
+    assert int(out.min()) == 143 and int(out.max()) == 143
+    out = DynamicImage(ImageBuffer(img)).blur_advanced(GaussianBlurParameters.new_from_sigma(10.0)).buf.data
+    assert int(out.min()) == 143 and int(out.max()) == 143

@@ -1,0 +1,175 @@
+"""GPU parity: the resampler through the C ABI against the oracle.
+STRICT flag: bit-exact.  FAST flag (FMA): +-1 LSB for u8/u16, 1e-5 relative for f32."""
+import numpy as np
+import pytest
+
+import oracle as o
+from conftest import bench_image, rand_image
+from image_b200 import FilterType, imageops
+from image_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+FILTERS = list(FilterType)
+
+
+def _check(img, nw, nh, f, cuda, acc_init=1.0, host=False, unfused=False):
+    import torch
+    want = o.resize(img, nw, nh, int(f), acc_init=acc_init)
+    extra = L.RESIZE_UNFUSED if unfused else 0
+    src = img if host else torch.from_numpy(img).to(cuda)
+    strict = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_STRICT | extra)
+    fast = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_FAST | extra)
+    if not host:
+        strict, fast = strict.cpu().numpy(), fast.cpu().numpy()
+    assert strict.shape == want.shape
+    assert strict.tobytes() == want.tobytes(), f"strict differs: {f.name} {img.shape}->{(nh, nw)} max|d|={np.abs(strict.astype(np.float64) - want).max()}"
+    if img.dtype == np.float32:
+        assert np.allclose(fast, want, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.abs(fast.astype(np.int64) - want.astype(np.int64)).max() <= 1
+    return fast, want
+
+
+@pytest.mark.parametrize("f", FILTERS)
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_resize_down_up_all_types(cuda, f, dtype, c):
+    rng = np.random.default_rng(c * 10 + int(f))
+    img = rand_image(rng, 61, 83, c, dtype)
+    for acc in (1.0, 0.0):
+        _check(img, 40, 29, f, cuda, acc_init=acc)     # down
+        _check(img, 131, 97, f, cuda, acc_init=acc)    # up
+    _check(img, 83, 20, f, cuda)                       # height only (horizontal pass still runs)
+    _check(img, 30, 61, f, cuda)                       # width only
+
+
+@pytest.mark.parametrize("f", FILTERS)
+def test_k1_shape(cuda, f):
+    """BASELINE config 1: 1920x1080 Rgba8 -> 960x540 (bench generator + alpha)."""
+    img = bench_image(1920, 1080, 4)
+    fast, want = _check(img, 960, 540, f, cuda)
+    if f == FilterType.Nearest:
+        assert np.array_equal(fast, want)
+
+
+@pytest.mark.parametrize("f", [FilterType.Nearest, FilterType.Triangle, FilterType.Lanczos3])
+def test_bench_shapes_rgb8(cuda, f):
+    """benches/imageops.rs:95-124: 1920x1080 Rgb8 -> 400x300 and (reduced) upscale."""
+    img = bench_image(1920, 1080, 3)
+    _check(img, 400, 300, f, cuda)
+    _check(img[:300, :400].copy(), 1000, 750, f, cuda)
+
+
+def test_k4_batch(cuda):
+    """BASELINE config 4 at a reduced batch: 1024x1024 Rgba8 -> 256x256 CatmullRom, one launch."""
+    import torch
+    rng = np.random.default_rng(4)
+    batch = rng.integers(0, 256, (3, 1024, 1024, 4), dtype=np.uint8)
+    got = imageops.resize_batch(torch.from_numpy(batch).to(cuda), 256, 256, FilterType.CatmullRom, flags=L.FP_STRICT).cpu().numpy()
+    for i in range(3):
+        assert np.array_equal(got[i], o.resize(batch[i], 256, 256, "catmullrom")), i
+
+
+def test_k5_band_f32_upscale(cuda):
+    """BASELINE config 5 on a crop: Rgba32F Lanczos3 2x upscale, literal and corrected modes."""
+    rng = np.random.default_rng(5)
+    img = rng.random((96, 160, 4), dtype=np.float32)
+    _check(img, 320, 192, FilterType.Lanczos3, cuda, acc_init=1.0)
+    fast, want = _check(img, 320, 192, FilterType.Lanczos3, cuda, acc_init=0.0)
+    assert want.min() >= 0 and want.max() <= 1 and want.std() > 0.1
+
+
+def test_band_entry_point(cuda):
+    """Row-band split: two bands with their halos reproduce the whole image bit for bit."""
+    import ctypes as C
+    import torch
+    rng = np.random.default_rng(6)
+    img = rng.random((120, 70, 4), dtype=np.float32)
+    nw, nh = 140, 240
+    want = o.resize(img, nw, nh, "lanczos3", acc_init=0.0)
+    lib = L.lib()
+    dev = torch.from_numpy(img).to(cuda)
+    out = torch.empty((nh, nw, 4), dtype=torch.float32, device=cuda)
+    for r0, rows in ((0, 100), (100, 140)):
+        s0, sn = C.c_uint32(), C.c_uint32()
+        L.check(lib.b200img_resize_band_src_rows(120, nh, 4, r0, rows, C.byref(s0), C.byref(sn)))
+        band = dev[s0.value:s0.value + sn.value].contiguous()
+        dst = torch.empty((rows, nw, 4), dtype=torch.float32, device=cuda)
+        L.check(lib.b200img_resize_band_dev(band.data_ptr(), s0.value, sn.value, 70, 120, 4, L.F32, dst.data_ptr(),
+                                            r0, rows, nw, nh, 4, 0.0, L.FP_STRICT, None))
+        out[r0:r0 + rows] = dst
+    assert out.cpu().numpy().tobytes() == want.tobytes()
+    # a band that lacks its halo is rejected
+    s0, sn = C.c_uint32(), C.c_uint32()
+    L.check(lib.b200img_resize_band_src_rows(120, nh, 4, 100, 140, C.byref(s0), C.byref(sn)))
+    assert lib.b200img_resize_band_dev(dev.data_ptr(), s0.value + 1, sn.value - 1, 70, 120, 4, L.F32, out.data_ptr(),
+                                       100, 140, nw, nh, 4, 0.0, 0, None) == L.ERR_BAD_ARG
+
+
+@pytest.mark.parametrize("f", FILTERS)
+def test_unfused_structure_matches(cuda, f):
+    rng = np.random.default_rng(8)
+    img = rand_image(rng, 50, 64, 3, np.uint8)
+    _check(img, 31, 23, f, cuda, unfused=True)
+    _check(rand_image(rng, 33, 20, 4, np.float32), 77, 50, f, cuda, unfused=True)
+
+
+def test_extreme_downscale_falls_back(cuda):
+    """bug_1600 (src/imageops/sample.rs:1892-1897): 629x627 -> 22x22 Lanczos3 is not all zero."""
+    img = np.full((627, 629, 4), 255, np.uint8)
+    fast, want = _check(img, 22, 22, FilterType.Lanczos3, cuda)
+    assert fast.any()
+    rng = np.random.default_rng(12)
+    _check(rand_image(rng, 900, 700, 3, np.uint8), 5, 3, FilterType.Gaussian, cuda)
+
+
+def test_edge_cases(cuda):
+    import torch
+    rng = np.random.default_rng(9)
+    img = rand_image(rng, 9, 11, 3, np.uint8)
+    # same size: copy (sample.rs:987-991)
+    assert np.array_equal(imageops.resize(torch.from_numpy(img).to(cuda), 11, 9, FilterType.Lanczos3).cpu().numpy(), img)
+    # empty source: zero-filled destination (977-984; issue_2340)
+    for shape in ((0, 5, 1), (5, 0, 1)):
+        z = imageops.resize(torch.zeros(shape, dtype=torch.uint8, device=cuda), 16, 16, FilterType.Lanczos3)
+        assert z.shape == (16, 16, 1) and not z.any()
+    # empty destination
+    assert imageops.resize(img, 0, 7, FilterType.Triangle).shape == (7, 0, 3)
+    # 1x1 source, 1-pixel destination, host-pointer path
+    _check(rand_image(rng, 1, 1, 4, np.uint16), 5, 3, FilterType.CatmullRom, cuda, host=True)
+    _check(img, 1, 1, FilterType.Lanczos3, cuda, host=True)
+    _check(rand_image(rng, 3, 200, 1, np.uint8), 333, 2, FilterType.Triangle, cuda, host=True)
+
+
+def test_resize_transparent_image_invariant(cuda):
+    """sample.rs:1861-1897: alpha never 253/254 in the centre, all filters (literal mode)."""
+    img = np.zeros((32, 32, 4), np.uint8)
+    img[4:28, 4:28] = [200, 100, 50, 255]
+    for f in FILTERS:
+        a = imageops.resize(img, 16, 16, f)[5:11, 5:11, 3]
+        assert not np.isin(a, [253, 254]).any(), f
+
+
+def test_nearest_roundtrip_identity(cuda):
+    """tests/regression.rs:154-174: Nearest 2x up then down is the identity (acc_init = 0)."""
+    rng = np.random.default_rng(2)
+    img = rand_image(rng, 66, 129, 4, np.uint8)
+    up = imageops.resize(img, 258, 132, FilterType.Nearest, acc_init=0.0)
+    assert np.array_equal(imageops.resize(up, 129, 66, FilterType.Nearest, acc_init=0.0), img)
+
+
+def test_large_image_linearity_property(cuda):
+    """Size-independent property on a large image (no oracle): resize of a constant image is the
+    constant (+acc_init), and Nearest output pixels are source pixels."""
+    import torch
+    img = torch.full((2160, 3840, 4), 77, dtype=torch.uint8, device=cuda)
+    out = imageops.resize(img, 1920, 1080, FilterType.Lanczos3, acc_init=0.0)
+    assert int(out.min()) >= 76 and int(out.max()) <= 78
+    g = torch.Generator(device=cuda).manual_seed(3)
+    rnd = torch.randint(0, 256, (2160, 3840, 4), dtype=torch.uint8, device=cuda, generator=g)
+    near = imageops.resize(rnd, 960, 540, FilterType.Nearest, acc_init=0.0)
+    l_v, _, _ = imageops.build_weights(FilterType.Nearest, 2160, 540, 0)
+    l_h, _, _ = imageops.build_weights(FilterType.Nearest, 3840, 960, 1)
+    idx_v = torch.from_numpy(l_v.astype(np.int64)).to(cuda)
+    idx_h = torch.from_numpy(l_h.astype(np.int64)).to(cuda)
+    assert torch.equal(near, rnd[idx_v][:, idx_h])
