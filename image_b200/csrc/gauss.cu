@@ -20,6 +20,14 @@
 #include <cstring>
 
 namespace b200 {
+
+// gauss_tiled.cu: register-tiled passes for reorderable sums (FAST f32 engine, Q0.15 engine)
+constexpr int GT_MAX_TAPS = 128;
+template <typename T, typename Mid, typename Acc>
+int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
+                    const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
+                    cudaStream_t st);
+
 namespace {
 
 constexpr int THREADS = 256;
@@ -160,6 +168,22 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
     void *mid;
     int rc = scratch(SCRATCH_A, total * mid_elem, &mid);
     if (rc) return rc;
+
+    const bool strict = (flags & B200IMG_FP_STRICT) != 0;
+    if ((q15 || !strict) && rk.size() <= (size_t)GT_MAX_TAPS && ck.size() <= (size_t)GT_MAX_TAPS) {
+        const int rl = (int)rk.size(), cl = (int)ck.size();
+#define TILED(T, Mid, Acc) \
+    return gauss_tiled_run<T, Mid, Acc>((const T *)src, (T *)dst, (Mid *)mid, w, h, C, n_images, rk.data(), rl, ck.data(), cl, \
+                                        g.row_shift, g.zero_first_row, st)
+        if (q15) {
+            if (dtype == B200IMG_U8) TILED(uint8_t, uint8_t, uint32_t);
+            TILED(uint16_t, uint16_t, uint32_t);
+        }
+        if (dtype == B200IMG_U8) TILED(uint8_t, float, float);
+        if (dtype == B200IMG_U16) TILED(uint16_t, float, float);
+        TILED(float, float, float);
+#undef TILED
+    }
 
     // weights travel in this stream's table scratch, ordered on the stream: back-to-back calls
     // with different kernels are safe (pageable source: staged before the call returns)

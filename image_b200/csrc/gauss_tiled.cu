@@ -1,0 +1,221 @@
+// gauss_tiled.cu -- the fast row / column passes of the separable convolution engine.
+//
+// Used when reordering the sum is allowed: the f32 engine under B200IMG_FP_FAST
+// (+-1 LSB contract) and the Q0.15 integer engine always (integer sums are exact
+// in any order, so it stays bit-identical to src/imageops/filter_1d.rs:171-390).
+//
+// Both passes are register-tiled 1-D convolutions: a thread produces R = 8
+// consecutive outputs along the filter axis from a sliding window of 15 staged
+// inputs, so each shared-memory load feeds 8 multiply-adds (LDS : FFMA = 1 : 8;
+// a per-output loop would be 1 : 1 and bound by the shared-memory pipe at a
+// quarter of the FP32 rate).  Weights sit in the kernel-parameter constant bank
+// and reach the FFMA/IMAD as uniform operands, costing no load slots.
+//   row pass:    lanes = 32 image rows (odd row pitch: conflict-free), warps =
+//                (8-pixel block, channel) pairs; results go through a staging
+//                buffer so global stores are row-contiguous.
+//   column pass: lanes = 32 consecutive subpixels of a row (coalesced loads and
+//                stores, conflict-free), thread = one column x 8 rows.
+// Clamp-to-edge (make_arena_row / make_columns_arenas, filter_1d.rs:60-130) is
+// applied while staging.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int GT_R = 8;           // outputs per thread along the filter axis
+constexpr int GT_MAX_TAPS = 128;  // longer kernels take the direct kernels in gauss.cu
+constexpr int GT_THREADS = 256;
+
+struct TapWeights { uint32_t w[GT_MAX_TAPS]; };  // f32 bits or Q0.15 integers, zero padded
+
+namespace {
+
+template <typename Acc> struct Arith;
+template <> struct Arith<float> {
+    static __device__ __forceinline__ float w(uint32_t b) { return __uint_as_float(b); }
+    static __device__ __forceinline__ float mac(float acc, float a, float b) { return __fmaf_rn(a, b, acc); }
+    static __device__ __forceinline__ uint32_t bits(float v) { return __float_as_uint(v); }
+    static __device__ __forceinline__ float from_bits(uint32_t b) { return __uint_as_float(b); }
+};
+template <> struct Arith<uint32_t> {
+    static __device__ __forceinline__ uint32_t w(uint32_t b) { return b; }
+    static __device__ __forceinline__ uint32_t mac(uint32_t acc, uint32_t a, uint32_t b) { return acc + a * b; }
+    static __device__ __forceinline__ uint32_t bits(uint32_t v) { return v; }
+    static __device__ __forceinline__ uint32_t from_bits(uint32_t b) { return b; }
+};
+
+// ToStorage (filter_1d.rs:132-164) / final nearest_from (sample.rs:1596-1601)
+template <typename Out, typename Acc> struct St;
+template <> struct St<uint8_t, uint32_t> { static __device__ __forceinline__ uint8_t f(uint32_t a) { return (uint8_t)min((a + 16384u) >> 15, 255u); } };
+template <> struct St<uint16_t, uint32_t> { static __device__ __forceinline__ uint16_t f(uint32_t a) { return (uint16_t)min((a + 16384u) >> 15, 65535u); } };
+template <> struct St<float, float> { static __device__ __forceinline__ float f(float a) { return a; } };
+template <> struct St<uint8_t, float> { static __device__ __forceinline__ uint8_t f(float a) { return Px<uint8_t>::nearest(a); } };
+template <> struct St<uint16_t, float> { static __device__ __forceinline__ uint16_t f(float a) { return Px<uint16_t>::nearest(a); } };
+
+// acc[r] = sum_k in[(r + k) * stride] * w[k], k < nch * 8.  `in` points at the first staged
+// input of output 0.  Window registers slide by 8 per chunk.
+template <typename Acc>
+__device__ __forceinline__ void conv8(const uint32_t *in, int stride, int nch, const TapWeights &tw, Acc (&acc)[GT_R]) {
+    using A = Arith<Acc>;
+    Acc win[2 * GT_R - 1];
+#pragma unroll
+    for (int i = 0; i < GT_R - 1; ++i) win[i] = A::from_bits(in[i * stride]);
+    in += (GT_R - 1) * stride;
+#pragma unroll 1
+    for (int ch = 0; ch < nch; ++ch) {
+#pragma unroll
+        for (int i = 0; i < GT_R; ++i) win[GT_R - 1 + i] = A::from_bits(in[i * stride]);
+        in += GT_R * stride;
+#pragma unroll
+        for (int kk = 0; kk < GT_R; ++kk) {
+            const Acc wk = A::w(tw.w[ch * GT_R + kk]);
+#pragma unroll
+            for (int r = 0; r < GT_R; ++r) acc[r] = A::mac(acc[r], win[r + kk], wk);
+        }
+#pragma unroll
+        for (int i = 0; i < GT_R - 1; ++i) win[i] = win[GT_R + i];
+    }
+}
+
+constexpr int ROW_XT = 64;    // output pixels per CTA tile (row pass)
+constexpr int ROW_ROWS = 32;  // rows per CTA tile = lanes
+
+// Row pass.  total_rows = rows of the whole batch (rows are independent).
+template <typename In, typename Mid, typename Acc>
+__global__ void __launch_bounds__(GT_THREADS)
+row_tiled_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, int C, size_t total_rows, int half,
+                 int shift, int nch, int in_pitch, int out_pitch, const __grid_constant__ TapWeights tw) {
+    using A = Arith<Acc>;
+    extern __shared__ __align__(16) uint32_t sm[];
+    uint32_t *s_in = sm;                                 // [ROW_ROWS][in_pitch]
+    uint32_t *s_out = sm + (size_t)ROW_ROWS * in_pitch;  // [ROW_ROWS][out_pitch]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int x0 = blockIdx.x * ROW_XT;
+    const size_t row0 = (size_t)blockIdx.y * ROW_ROWS;
+    const int sp = ROW_XT + nch * GT_R - 1;  // staged pixels per row
+    const int row_elems = sp * C;
+    const size_t g_pitch = (size_t)W * C;
+
+    for (int i = tid; i < ROW_ROWS * row_elems; i += GT_THREADS) {
+        const int r = i / row_elems, e = i - r * row_elems;
+        const int p = e / C, c = e - p * C;
+        const int px = min(max(x0 - half - shift + p, 0), (int)W - 1);
+        const size_t row = min(row0 + r, total_rows - 1);
+        s_in[r * in_pitch + e] = A::bits((Acc)src[row * g_pitch + (size_t)px * C + c]);
+    }
+    __syncthreads();
+
+    const int items = (ROW_XT / GT_R) * C;
+    for (int item = warp; item < items; item += GT_THREADS / 32) {
+        const int xb = item / C, c = item - xb * C;
+        Acc acc[GT_R];
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) acc[r] = (Acc)0;
+        conv8<Acc>(s_in + lane * in_pitch + (xb * GT_R) * C + c, C, nch, tw, acc);
+        uint32_t *o = s_out + lane * out_pitch + (xb * GT_R) * C + c;
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) {
+            if constexpr (sizeof(Mid) == 4) o[r * C] = A::bits(acc[r]);
+            else o[r * C] = (uint32_t)St<Mid, Acc>::f(acc[r]);
+        }
+    }
+    __syncthreads();
+
+    const int out_elems = min(ROW_XT, (int)W - x0) * C;
+    for (int i = tid; i < ROW_ROWS * out_elems; i += GT_THREADS) {
+        const int r = i / out_elems, e = i - r * out_elems;
+        const size_t row = row0 + r;
+        if (row < total_rows) {
+            const uint32_t v = s_out[r * out_pitch + e];
+            Mid *g = mid + row * g_pitch + (size_t)x0 * C + e;
+            if (sizeof(Mid) == 4) *reinterpret_cast<uint32_t *>(g) = v;
+            else *g = (Mid)v;
+        }
+    }
+}
+
+constexpr int COL_TH = 128;  // output rows per CTA tile (column pass)
+constexpr int COL_TW = 64;   // subpixel columns per CTA tile
+
+template <typename Mid, typename Out, typename Acc>
+__global__ void __launch_bounds__(GT_THREADS)
+col_tiled_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
+                 int nch, int zero_first_row, const __grid_constant__ TapWeights tw) {
+    using A = Arith<Acc>;
+    extern __shared__ __align__(16) uint32_t sm[];  // [COL_TH + nch*8 - 1][COL_TW]
+    const int tid = threadIdx.x;
+    const uint32_t s0 = blockIdx.x * COL_TW;
+    const uint32_t img = blockIdx.y / tiles_y;
+    const int y0 = (int)(blockIdx.y % tiles_y) * COL_TH;
+    const int sr = COL_TH + nch * GT_R - 1;
+    const Mid *m = mid + (size_t)img * H * row_sub;
+
+    for (int i = tid; i < sr * COL_TW; i += GT_THREADS) {
+        const int r = i / COL_TW, s = i - r * COL_TW;
+        const int y = min(max(y0 - half + r, 0), (int)H - 1);
+        const uint32_t col = min(s0 + s, row_sub - 1);
+        sm[i] = A::bits((Acc)m[(size_t)y * row_sub + col]);
+    }
+    __syncthreads();
+
+    Out *d = dst + (size_t)img * H * row_sub;
+    for (int item = tid; item < COL_TW * (COL_TH / GT_R); item += GT_THREADS) {
+        const int s = item % COL_TW, rb = item / COL_TW;
+        Acc acc[GT_R];
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) acc[r] = (Acc)0;
+        conv8<Acc>(sm + (rb * GT_R) * COL_TW + s, COL_TW, nch, tw, acc);
+        if (s0 + s < row_sub) {
+#pragma unroll
+            for (int r = 0; r < GT_R; ++r) {
+                const int y = y0 + rb * GT_R + r;
+                if (y < (int)H) d[(size_t)y * row_sub + s0 + s] = (zero_first_row && y == 0) ? (Out)0 : St<Out, Acc>::f(acc[r]);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+// Launches both passes.  rk / ck are the scanned kernels (f32 bits or Q0.15), lengths odd <= 128.
+template <typename T, typename Mid, typename Acc>
+int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
+                    const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
+                    cudaStream_t st) {
+    TapWeights rw, cw;
+    for (int i = 0; i < GT_MAX_TAPS; ++i) { rw.w[i] = i < rlen ? rk[i] : 0u; cw.w[i] = i < clen ? ck[i] : 0u; }
+    const int rnch = (rlen + GT_R - 1) / GT_R, cnch = (clen + GT_R - 1) / GT_R;
+    const size_t total_rows = (size_t)h * n_images;
+
+    {
+        const int sp = ROW_XT + rnch * GT_R - 1;
+        const int in_pitch = (sp * C) | 1, out_pitch = (ROW_XT * C) | 1;
+        const size_t smem = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
+        auto k = row_tiled_kernel<T, Mid, Acc>;
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const dim3 grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
+        k<<<grid, GT_THREADS, smem, st>>>(src, mid, w, C, total_rows, rlen / 2, row_shift, rnch, in_pitch, out_pitch, rw);
+    }
+    {
+        const uint32_t row_sub = w * (uint32_t)C;
+        const int tiles_y = (int)((h + COL_TH - 1) / COL_TH);
+        const size_t smem = (size_t)(COL_TH + cnch * GT_R - 1) * COL_TW * 4;
+        auto k = col_tiled_kernel<Mid, T, Acc>;
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const dim3 grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
+        k<<<grid, GT_THREADS, smem, st>>>(mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cw);
+    }
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
+#define INST(T, Mid, Acc)                                                                                              \
+    template int gauss_tiled_run<T, Mid, Acc>(const T *, T *, Mid *, uint32_t, uint32_t, int, uint32_t, const uint32_t *, \
+                                              int, const uint32_t *, int, int, int, cudaStream_t);
+INST(uint8_t, float, float)
+INST(uint16_t, float, float)
+INST(float, float, float)
+INST(uint8_t, uint8_t, uint32_t)
+INST(uint16_t, uint16_t, uint32_t)
+#undef INST
+
+}  // namespace b200
