@@ -1,16 +1,26 @@
 // boxblur.cu -- imageops::fast_blur: three box blurs (Kovesi), each a horizontal
-// then a vertical pass that stores back to the pixel type.
+// then a vertical sliding-sum pass that stores back to the pixel type.
 //
 // Reference: src/imageops/fast_blur.rs -- fast_blur 111-191, boxes_for_gauss
 // 201-226, box_blur_horizontal_pass 303-413, box_blur_vertical_pass 416-473,
 // accumulators 36-94 (u8: u32 sums and an exact multiply-shift division; other
 // types: f32 sums times 1/ks, then clamp_nearest_from).
 //
-// The reference slides one running sum along each row / column.  A window sum
-// of integers is the same number in any order, so for u8 (u32 sums) and for
-// u16 while ks * 65535 < 2^24 (f32 sums of integers below 2^24 are exact) the
-// result here is bit-identical.  For f32 pixels the running sum's rounding
-// history is not reproduced; results agree to f32 round-off.
+// The reference slides one running sum along each whole row / column.  A window
+// sum of integers is the same number however it is accumulated, so u8 (u32
+// sums) and u16 while ks * 65535 < 2^24 (the reference's f32 sums of integers
+// below 2^24 are exact) come out bit-identical even though the sums here are
+// restarted per tile.  For f32 pixels, and u16 with kernels beyond 257 taps, the
+// reference's rounding history along the whole row is not reproducible by any
+// parallel schedule; those agree to f32 round-off.
+//
+//   vertical pass:   thread = one 32-bit word of a row (4 u8 / 2 u16 / 1 f32
+//                    subpixels) x a band of rows; the running sums live in
+//                    registers, loads and stores are fully coalesced.
+//   horizontal pass: a CTA stages 32 rows x a span of pixels in shared memory;
+//                    lane = row (row pitch = odd number of words: conflict-free),
+//                    each lane slides its sums along a 64-pixel chunk; results go
+//                    back through shared memory so global stores are contiguous.
 #include "common.cuh"
 #include "host_tables.h"
 
@@ -19,40 +29,176 @@ namespace {
 
 constexpr int THREADS = 256;
 
+struct BoxGeom {
+    uint32_t w, h, C;
+    uint32_t r, ks, recip, bias;  // radius, 2r+1, ceil(2^32 / ks), ks / 2
+    float inv;                    // 1.0f / ks
+};
+
+// per-type sum / store rules
 template <typename T> struct Box;
 template <> struct Box<uint8_t> {
-    typedef uint32_t acc_t;
+    typedef uint32_t sum_t;
     static __device__ __forceinline__ uint32_t lift(uint8_t v) { return v; }
     // to_store, fast_blur.rs:66-70: ((acc + ks/2) * ceil(2^32/ks)) >> 32
-    static __device__ __forceinline__ uint8_t store(uint32_t acc, uint32_t ks, uint32_t recip, float) {
-        return (uint8_t)__umulhi(acc + ks / 2u, recip);
-    }
+    static __device__ __forceinline__ uint8_t store(uint32_t s, const BoxGeom &g) { return (uint8_t)__umulhi(s + g.bias, g.recip); }
 };
 template <> struct Box<uint16_t> {
-    typedef float acc_t;
-    static __device__ __forceinline__ float lift(uint16_t v) { return (float)v; }
-    static __device__ __forceinline__ uint16_t store(float acc, uint32_t, uint32_t, float inv) {
-        return Px<uint16_t>::clamp_nearest(__fmul_rn(acc, inv));
+    typedef uint32_t sum_t;  // integer sums: equal to the reference's f32 sums while those are exact
+    static __device__ __forceinline__ uint32_t lift(uint16_t v) { return v; }
+    static __device__ __forceinline__ uint16_t store(uint32_t s, const BoxGeom &g) {
+        return Px<uint16_t>::clamp_nearest(__fmul_rn((float)s, g.inv));
     }
 };
 template <> struct Box<float> {
-    typedef float acc_t;
+    typedef float sum_t;
     static __device__ __forceinline__ float lift(float v) { return v; }
-    static __device__ __forceinline__ float store(float acc, uint32_t, uint32_t, float inv) {
-        return Px<float>::clamp_nearest(__fmul_rn(acc, inv));
-    }
+    static __device__ __forceinline__ float store(float s, const BoxGeom &g) { return Px<float>::clamp_nearest(__fmul_rn(s, g.inv)); }
 };
 
-struct BoxGeom {
-    uint32_t w, h, C;
-    uint32_t r, ks, recip;  // radius, 2r+1, ceil(2^32 / ks)
-    float inv;              // 1.0f / ks
-};
+// ---- vertical pass ---------------------------------------------------------------------
+constexpr int V_BAND = 64;  // rows per thread
 
-// window sum along x with clamp-to-edge: sum_{d=-r..r} p[clamp(x+d)]
-template <typename T, typename B>
+template <typename T>
 __global__ void __launch_bounds__(THREADS)
-box_h_kernel(const T *src, T *dst, BoxGeom g, size_t total) {
+box_v_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, uint32_t n_images, int bands) {
+    typedef typename Box<T>::sum_t S;
+    constexpr int N = 4 / sizeof(T);  // subpixels per 32-bit word
+    const size_t row_sub = (size_t)g.w * g.C;
+    const uint32_t words = (uint32_t)((row_sub + N - 1) / N);
+    const uint32_t wd = blockIdx.x * THREADS + threadIdx.x;
+    if (wd >= words) return;
+    const uint32_t img = blockIdx.y / bands, band = blockIdx.y % bands;
+    const int y0 = (int)band * V_BAND, y1 = min(y0 + V_BAND, (int)g.h);
+    const int r = (int)g.r, hmax = (int)g.h - 1;
+    const T *p = src + (size_t)img * g.h * row_sub;
+    T *d = dst + (size_t)img * g.h * row_sub;
+    const size_t s0 = (size_t)wd * N;
+    const int n = (int)min((size_t)N, row_sub - s0);  // ragged last word
+    // whole words only when every row start is word aligned
+    const bool vec = n == N && (row_sub * sizeof(T)) % 4 == 0 && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(d)) & 3) == 0;
+
+    auto load = [&](int y, S (&v)[N]) {
+        const T *q = p + (size_t)y * row_sub + s0;
+        if (vec) {
+            const uint32_t wv = *reinterpret_cast<const uint32_t *>(q);
+            if constexpr (N == 4) { v[0] = wv & 0xff; v[1] = (wv >> 8) & 0xff; v[2] = (wv >> 16) & 0xff; v[3] = wv >> 24; }
+            else if constexpr (N == 2) { v[0] = wv & 0xffff; v[1] = wv >> 16; }
+            else v[0] = __uint_as_float(wv);
+        } else {
+#pragma unroll
+            for (int j = 0; j < N; ++j) v[j] = j < n ? Box<T>::lift(q[j]) : (S)0;
+        }
+    };
+
+    // sums for row y0: sum_{d=-r..r} p[clamp(y0 + d)]
+    S sum[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) sum[j] = (S)0;
+    {
+        const int lo = y0 - r, hi = y0 + r;
+        const int nlo = lo < 0 ? -lo : 0, nhi = hi > hmax ? hi - hmax : 0;
+        S v[N];
+        for (int y = max(lo, 0); y <= min(hi, hmax); ++y) {
+            load(y, v);
+#pragma unroll
+            for (int j = 0; j < N; ++j) sum[j] += v[j];
+        }
+        if (nlo) { load(0, v);
+#pragma unroll
+            for (int j = 0; j < N; ++j) sum[j] += v[j] * (S)nlo; }
+        if (nhi) { load(hmax, v);
+#pragma unroll
+            for (int j = 0; j < N; ++j) sum[j] += v[j] * (S)nhi; }
+    }
+    for (int y = y0; y < y1; ++y) {
+        T o[N];
+#pragma unroll
+        for (int j = 0; j < N; ++j) o[j] = Box<T>::store(sum[j], g);
+        T *q = d + (size_t)y * row_sub + s0;
+        if (vec) {
+            uint32_t wv;
+            if constexpr (N == 4) wv = (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16) | ((uint32_t)o[3] << 24);
+            else if constexpr (N == 2) wv = (uint32_t)o[0] | ((uint32_t)o[1] << 16);
+            else wv = __float_as_uint(o[0]);
+            *reinterpret_cast<uint32_t *>(q) = wv;
+        } else {
+#pragma unroll
+            for (int j = 0; j < N; ++j) if (j < n) q[j] = o[j];
+        }
+        S a[N], b[N];
+        load(min(y + r + 1, hmax), a);
+        load(max(y - r, 0), b);
+#pragma unroll
+        for (int j = 0; j < N; ++j) sum[j] = sum[j] + a[j] - b[j];  // the reference's order: add, then subtract
+    }
+}
+
+// ---- horizontal pass ---------------------------------------------------------------------
+constexpr int H_ROWS = 32;  // rows per CTA tile = lanes
+constexpr int H_XT = 256;   // output pixels per CTA tile
+constexpr int H_XC = 64;    // pixels per thread chunk
+
+template <typename T, int C>
+__global__ void __launch_bounds__(THREADS)
+box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t total_rows, int in_pitch, int out_pitch) {
+    typedef typename Box<T>::sum_t S;
+    extern __shared__ __align__(16) unsigned char smem[];
+    T *s_in = reinterpret_cast<T *>(smem);                                    // [H_ROWS][in_pitch]   (pitch in elements)
+    T *s_out = reinterpret_cast<T *>(smem) + (size_t)H_ROWS * in_pitch;        // [H_ROWS][out_pitch]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int x0 = blockIdx.x * H_XT;
+    const size_t row0 = (size_t)blockIdx.y * H_ROWS;
+    const int r = (int)g.r, W = (int)g.w;
+    const int tw = min(H_XT, W - x0);
+    const int sp = tw + 2 * r;  // staged pixels: x0 - r .. x0 + tw - 1 + r, clamped
+    const size_t g_pitch = (size_t)W * C;
+    const bool interior = x0 - r >= 0 && x0 + tw + r <= W;
+
+    for (int rr = warp; rr < H_ROWS; rr += THREADS / 32) {
+        const T *grow = src + min(row0 + rr, total_rows - 1) * g_pitch;
+        T *s = s_in + (size_t)rr * in_pitch;
+        if (interior) {
+            const T *q = grow + (size_t)(x0 - r) * C;
+            for (int e = lane; e < sp * C; e += 32) s[e] = q[e];
+        } else {
+            for (int e = lane; e < sp * C; e += 32) {
+                const int p = e / C, c = e - p * C;
+                s[e] = grow[(size_t)min(max(x0 - r + p, 0), W - 1) * C + c];
+            }
+        }
+    }
+    __syncthreads();
+
+    const int chunks = (tw + H_XC - 1) / H_XC;
+    for (int item = warp; item < chunks * C; item += THREADS / 32) {
+        const int ck = item / C, c = item - ck * C;
+        const int xa = ck * H_XC, xb = min(xa + H_XC, tw);  // outputs [xa, xb) of this tile
+        const T *in = s_in + (size_t)lane * in_pitch + c;    // staged pixel j <-> source pixel x0 - r + j
+        T *out = s_out + (size_t)lane * out_pitch + c;
+        S sum = (S)0;
+        for (int j = xa; j <= xa + 2 * r; ++j) sum += Box<T>::lift(in[j * C]);  // window of output xa
+        for (int x = xa; x < xb; ++x) {
+            out[x * C] = Box<T>::store(sum, g);
+            sum = sum + Box<T>::lift(in[(x + 2 * r + 1) * C]) - Box<T>::lift(in[x * C]);
+        }
+    }
+    __syncthreads();
+
+    for (int rr = warp; rr < H_ROWS; rr += THREADS / 32) {
+        const size_t row = row0 + rr;
+        if (row >= total_rows) break;
+        T *q = dst + row * g_pitch + (size_t)x0 * C;
+        const T *s = s_out + (size_t)rr * out_pitch;
+        for (int e = lane; e < tw * C; e += 32) q[e] = s[e];
+    }
+}
+
+// Fallback for radii whose staged tile does not fit shared memory: direct window sum per output.
+template <typename T>
+__global__ void __launch_bounds__(THREADS)
+box_h_direct_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t total) {
+    typedef typename Box<T>::sum_t S;
     const size_t row_sub = (size_t)g.w * g.C;
     const int wmax = (int)g.w - 1, r = (int)g.r;
     for (size_t idx = (size_t)blockIdx.x * THREADS + threadIdx.x; idx < total; idx += (size_t)gridDim.x * THREADS) {
@@ -60,47 +206,27 @@ box_h_kernel(const T *src, T *dst, BoxGeom g, size_t total) {
         const uint32_t s = (uint32_t)(idx - row * row_sub);
         const int x = (int)(s / g.C), c = (int)(s - (uint32_t)x * g.C);
         const T *p = src + row * row_sub + c;
-        typename B::acc_t acc = 0;
-        // replicated edges contribute count * edge value; the interior is a plain sum
         const int lo = x - r, hi = x + r;
-        const int nlo = lo < 0 ? -lo : 0;           // taps clamped to column 0
-        const int nhi = hi > wmax ? hi - wmax : 0;  // taps clamped to column w-1
-        const int a = max(lo, 0), b = min(hi, wmax);
-        for (int xx = a; xx <= b; ++xx) acc += B::lift(p[(size_t)xx * g.C]);
-        if (nlo) acc += B::lift(p[0]) * (typename B::acc_t)nlo;
-        if (nhi) acc += B::lift(p[(size_t)wmax * g.C]) * (typename B::acc_t)nhi;
-        dst[idx] = B::store(acc, g.ks, g.recip, g.inv);
+        const int nlo = lo < 0 ? -lo : 0, nhi = hi > wmax ? hi - wmax : 0;
+        S acc = (S)0;
+        for (int xx = max(lo, 0); xx <= min(hi, wmax); ++xx) acc += Box<T>::lift(p[(size_t)xx * g.C]);
+        if (nlo) acc += Box<T>::lift(p[0]) * (S)nlo;
+        if (nhi) acc += Box<T>::lift(p[(size_t)wmax * g.C]) * (S)nhi;
+        dst[idx] = Box<T>::store(acc, g);
     }
 }
 
-template <typename T, typename B>
-__global__ void __launch_bounds__(THREADS)
-box_v_kernel(const T *src, T *dst, BoxGeom g, size_t total) {
-    const size_t row_sub = (size_t)g.w * g.C;
-    const int hmax = (int)g.h - 1, r = (int)g.r;
-    for (size_t idx = (size_t)blockIdx.x * THREADS + threadIdx.x; idx < total; idx += (size_t)gridDim.x * THREADS) {
-        const size_t row = idx / row_sub;
-        const size_t s = idx - row * row_sub;
-        const size_t img = row / g.h;
-        const int y = (int)(row - img * g.h);
-        const T *p = src + img * (size_t)g.h * row_sub + s;
-        typename B::acc_t acc = 0;
-        const int lo = y - r, hi = y + r;
-        const int nlo = lo < 0 ? -lo : 0;
-        const int nhi = hi > hmax ? hi - hmax : 0;
-        const int a = max(lo, 0), b = min(hi, hmax);
-        for (int yy = a; yy <= b; ++yy) acc += B::lift(p[(size_t)yy * row_sub]);
-        if (nlo) acc += B::lift(p[0]) * (typename B::acc_t)nlo;
-        if (nhi) acc += B::lift(p[(size_t)hmax * row_sub]) * (typename B::acc_t)nhi;
-        dst[idx] = B::store(acc, g.ks, g.recip, g.inv);
-    }
+// pitch (in elements of T) >= n with an odd number of 32-bit words per row
+int odd_word_pitch(int n, int tsize) {
+    int words = (n * tsize + 3) / 4;
+    words |= 1;
+    return words * 4 / tsize;
 }
 
 template <typename T>
 int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, uint32_t n_images, const uint32_t radii[3],
-        int sm_count, cudaStream_t st) {
-    const size_t total = (size_t)w * h * C * n_images;
-    const unsigned grid = (unsigned)std::min<size_t>((total + THREADS - 1) / THREADS, (size_t)sm_count * 32);
+        const DeviceCtx *ctx, cudaStream_t st) {
+    const size_t total_rows = (size_t)h * n_images;
     const T *cur = (const T *)src;
     for (int pass = 0; pass < 3; ++pass) {
         BoxGeom g;
@@ -108,9 +234,40 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
         g.r = radii[pass];
         g.ks = 2 * g.r + 1;
         g.recip = UINT32_MAX / g.ks + 1u;
+        g.bias = g.ks / 2;
         g.inv = 1.0f / (float)g.ks;
-        box_h_kernel<T, Box<T>><<<grid, THREADS, 0, st>>>(cur, (T *)tmp, g, total);
-        box_v_kernel<T, Box<T>><<<grid, THREADS, 0, st>>>((const T *)tmp, (T *)dst, g, total);
+        {
+            // one staged element past the last window keeps the sliding update branch-free
+            const int in_pitch = odd_word_pitch((H_XT + 2 * (int)g.r + 1) * C, sizeof(T));
+            const int out_pitch = odd_word_pitch(H_XT * C, sizeof(T));
+            const size_t smem = (size_t)H_ROWS * (in_pitch + out_pitch) * sizeof(T);
+            const dim3 grid((w + H_XT - 1) / H_XT, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
+            if (smem > ctx->smem_optin) {
+                const size_t total = total_rows * w * C;
+                const unsigned gd = (unsigned)std::min<size_t>((total + THREADS - 1) / THREADS, (size_t)ctx->sm_count * 32);
+                box_h_direct_kernel<T><<<gd, THREADS, 0, st>>>(cur, (T *)tmp, g, total);
+            } else
+#define H_GO(CC)                                                                                            \
+    {                                                                                                       \
+        auto k = box_h_kernel<T, CC>;                                                                       \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));         \
+        k<<<grid, THREADS, smem, st>>>(cur, (T *)tmp, g, total_rows, in_pitch, out_pitch);                  \
+    }
+            switch (C) {
+                case 1: H_GO(1) break;
+                case 2: H_GO(2) break;
+                case 3: H_GO(3) break;
+                default: H_GO(4) break;
+            }
+#undef H_GO
+        }
+        {
+            constexpr int N = 4 / sizeof(T);
+            const uint32_t words = (uint32_t)(((size_t)w * C + N - 1) / N);
+            const int bands = (int)((h + V_BAND - 1) / V_BAND);
+            const dim3 grid((words + THREADS - 1) / THREADS, (unsigned)(bands * n_images));
+            box_v_kernel<T><<<grid, THREADS, 0, st>>>((const T *)tmp, (T *)dst, g, n_images, bands);
+        }
         cur = (const T *)dst;
     }
     B200_CUDA(cudaGetLastError());
@@ -125,9 +282,10 @@ int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
     if (!ctx) return B200IMG_ERR_CUDA;
     uint32_t radii[3];
     boxes_for_gauss(sigma, radii);
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 3; ++i) {
         if (radii[i] >= (1u << 23))  // beyond here the reference's u8 path switches accumulators (fast_blur.rs:238-247)
             return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur: box radius %u is beyond the supported range", radii[i]);
+    }
     size_t bytes;
     if (!checked_mul((size_t)w * h, (size_t)C, dtype_size(dtype), n_images, &bytes))
         return fail(B200IMG_ERR_DIMENSION, "fast_blur: size overflows");
@@ -135,9 +293,9 @@ int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
     int rc = scratch(SCRATCH_A, bytes, &tmp);
     if (rc) return rc;
     switch (dtype) {
-        case B200IMG_U8: return run<uint8_t>(src, dst, tmp, w, h, C, n_images, radii, ctx->sm_count, st);
-        case B200IMG_U16: return run<uint16_t>(src, dst, tmp, w, h, C, n_images, radii, ctx->sm_count, st);
-        default: return run<float>(src, dst, tmp, w, h, C, n_images, radii, ctx->sm_count, st);
+        case B200IMG_U8: return run<uint8_t>(src, dst, tmp, w, h, C, n_images, radii, ctx, st);
+        case B200IMG_U16: return run<uint16_t>(src, dst, tmp, w, h, C, n_images, radii, ctx, st);
+        default: return run<float>(src, dst, tmp, w, h, C, n_images, radii, ctx, st);
     }
 }
 

@@ -51,25 +51,30 @@ template <> struct St<float, float> { static __device__ __forceinline__ float f(
 template <> struct St<uint8_t, float> { static __device__ __forceinline__ uint8_t f(float a) { return Px<uint8_t>::nearest(a); } };
 template <> struct St<uint16_t, float> { static __device__ __forceinline__ uint16_t f(float a) { return Px<uint16_t>::nearest(a); } };
 
-// acc[r] = sum_k in[(r + k) * stride] * w[k], k < nch * 8.  `in` points at the first staged
-// input of output 0.  Window registers slide by 8 per chunk.
-template <typename Acc>
-__device__ __forceinline__ void conv8(const uint32_t *in, int stride, int nch, const TapWeights &tw, Acc (&acc)[GT_R]) {
+// acc[r] = sum_k in[(r + k) * STRIDE] * w[k], k < nch * 8.  `in` points at the first staged
+// input of output 0.  Window registers slide by 8 per chunk.  STRIDE is a compile-time
+// constant so every LDS carries an immediate offset (no address arithmetic in the loop).
+template <typename Acc, int STRIDE>
+__device__ __forceinline__ void conv8(const uint32_t *in, int nch, const TapWeights &tw, Acc (&acc)[GT_R]) {
     using A = Arith<Acc>;
     Acc win[2 * GT_R - 1];
 #pragma unroll
-    for (int i = 0; i < GT_R - 1; ++i) win[i] = A::from_bits(in[i * stride]);
-    in += (GT_R - 1) * stride;
+    for (int i = 0; i < GT_R - 1; ++i) win[i] = A::from_bits(in[i * STRIDE]);
+    in += (GT_R - 1) * STRIDE;
+    const uint2 *w2 = reinterpret_cast<const uint2 *>(tw.w);
 #pragma unroll 1
     for (int ch = 0; ch < nch; ++ch) {
 #pragma unroll
-        for (int i = 0; i < GT_R; ++i) win[GT_R - 1 + i] = A::from_bits(in[i * stride]);
-        in += GT_R * stride;
+        for (int i = 0; i < GT_R; ++i) win[GT_R - 1 + i] = A::from_bits(in[i * STRIDE]);
+        in += GT_R * STRIDE;
 #pragma unroll
-        for (int kk = 0; kk < GT_R; ++kk) {
-            const Acc wk = A::w(tw.w[ch * GT_R + kk]);
+        for (int kp = 0; kp < GT_R / 2; ++kp) {
+            const uint2 wv = w2[ch * (GT_R / 2) + kp];
+            const Acc wa = A::w(wv.x), wb = A::w(wv.y);
 #pragma unroll
-            for (int r = 0; r < GT_R; ++r) acc[r] = A::mac(acc[r], win[r + kk], wk);
+            for (int r = 0; r < GT_R; ++r) acc[r] = A::mac(acc[r], win[r + 2 * kp], wa);
+#pragma unroll
+            for (int r = 0; r < GT_R; ++r) acc[r] = A::mac(acc[r], win[r + 2 * kp + 1], wb);
         }
 #pragma unroll
         for (int i = 0; i < GT_R - 1; ++i) win[i] = win[GT_R + i];
@@ -80,38 +85,48 @@ constexpr int ROW_XT = 64;    // output pixels per CTA tile (row pass)
 constexpr int ROW_ROWS = 32;  // rows per CTA tile = lanes
 
 // Row pass.  total_rows = rows of the whole batch (rows are independent).
-template <typename In, typename Mid, typename Acc>
+template <typename In, typename Mid, typename Acc, int C>
 __global__ void __launch_bounds__(GT_THREADS)
-row_tiled_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, int C, size_t total_rows, int half,
-                 int shift, int nch, int in_pitch, int out_pitch, const __grid_constant__ TapWeights tw) {
+row_tiled_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, size_t total_rows, int half,
+                 int shift, int nch, int in_pitch, const __grid_constant__ TapWeights tw) {
     using A = Arith<Acc>;
+    constexpr int OUT_PITCH = (ROW_XT * C) | 1;
     extern __shared__ __align__(16) uint32_t sm[];
     uint32_t *s_in = sm;                                 // [ROW_ROWS][in_pitch]
-    uint32_t *s_out = sm + (size_t)ROW_ROWS * in_pitch;  // [ROW_ROWS][out_pitch]
+    uint32_t *s_out = sm + (size_t)ROW_ROWS * in_pitch;  // [ROW_ROWS][OUT_PITCH]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int x0 = blockIdx.x * ROW_XT;
     const size_t row0 = (size_t)blockIdx.y * ROW_ROWS;
     const int sp = ROW_XT + nch * GT_R - 1;  // staged pixels per row
     const int row_elems = sp * C;
     const size_t g_pitch = (size_t)W * C;
+    const int xs = x0 - half - shift;  // source pixel of staged pixel 0
+    const bool interior = xs >= 0 && xs + sp <= (int)W;
 
-    for (int i = tid; i < ROW_ROWS * row_elems; i += GT_THREADS) {
-        const int r = i / row_elems, e = i - r * row_elems;
-        const int p = e / C, c = e - p * C;
-        const int px = min(max(x0 - half - shift + p, 0), (int)W - 1);
-        const size_t row = min(row0 + r, total_rows - 1);
-        s_in[r * in_pitch + e] = A::bits((Acc)src[row * g_pitch + (size_t)px * C + c]);
+    for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
+        const In *g = src + min(row0 + r, total_rows - 1) * g_pitch;
+        uint32_t *s = s_in + r * in_pitch;
+        if (interior) {
+            g += (size_t)xs * C;
+            for (int e = lane; e < row_elems; e += 32) s[e] = A::bits((Acc)g[e]);
+        } else {
+            for (int e = lane; e < row_elems; e += 32) {
+                const int p = e / C, c = e - p * C;
+                const int px = min(max(xs + p, 0), (int)W - 1);
+                s[e] = A::bits((Acc)g[(size_t)px * C + c]);
+            }
+        }
     }
     __syncthreads();
 
-    const int items = (ROW_XT / GT_R) * C;
-    for (int item = warp; item < items; item += GT_THREADS / 32) {
+    constexpr int ITEMS = (ROW_XT / GT_R) * C;
+    for (int item = warp; item < ITEMS; item += GT_THREADS / 32) {
         const int xb = item / C, c = item - xb * C;
         Acc acc[GT_R];
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) acc[r] = (Acc)0;
-        conv8<Acc>(s_in + lane * in_pitch + (xb * GT_R) * C + c, C, nch, tw, acc);
-        uint32_t *o = s_out + lane * out_pitch + (xb * GT_R) * C + c;
+        conv8<Acc, C>(s_in + lane * in_pitch + (xb * GT_R) * C + c, nch, tw, acc);
+        uint32_t *o = s_out + lane * OUT_PITCH + (xb * GT_R) * C + c;
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) {
             if constexpr (sizeof(Mid) == 4) o[r * C] = A::bits(acc[r]);
@@ -121,14 +136,14 @@ row_tiled_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
     __syncthreads();
 
     const int out_elems = min(ROW_XT, (int)W - x0) * C;
-    for (int i = tid; i < ROW_ROWS * out_elems; i += GT_THREADS) {
-        const int r = i / out_elems, e = i - r * out_elems;
+    for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
         const size_t row = row0 + r;
-        if (row < total_rows) {
-            const uint32_t v = s_out[r * out_pitch + e];
-            Mid *g = mid + row * g_pitch + (size_t)x0 * C + e;
-            if (sizeof(Mid) == 4) *reinterpret_cast<uint32_t *>(g) = v;
-            else *g = (Mid)v;
+        if (row >= total_rows) break;
+        Mid *g = mid + row * g_pitch + (size_t)x0 * C;
+        const uint32_t *s = s_out + r * OUT_PITCH;
+        for (int e = lane; e < out_elems; e += 32) {
+            if constexpr (sizeof(Mid) == 4) reinterpret_cast<uint32_t *>(g)[e] = s[e];
+            else g[e] = (Mid)s[e];
         }
     }
 }
@@ -149,11 +164,14 @@ col_tiled_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
     const int sr = COL_TH + nch * GT_R - 1;
     const Mid *m = mid + (size_t)img * H * row_sub;
 
-    for (int i = tid; i < sr * COL_TW; i += GT_THREADS) {
-        const int r = i / COL_TW, s = i - r * COL_TW;
-        const int y = min(max(y0 - half + r, 0), (int)H - 1);
+    {
+        static_assert(GT_THREADS % COL_TW == 0, "one staging thread per column");
+        const int s = tid % COL_TW;
         const uint32_t col = min(s0 + s, row_sub - 1);
-        sm[i] = A::bits((Acc)m[(size_t)y * row_sub + col]);
+        for (int r = tid / COL_TW; r < sr; r += GT_THREADS / COL_TW) {
+            const int y = min(max(y0 - half + r, 0), (int)H - 1);
+            sm[r * COL_TW + s] = A::bits((Acc)m[(size_t)y * row_sub + col]);
+        }
     }
     __syncthreads();
 
@@ -163,7 +181,7 @@ col_tiled_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
         Acc acc[GT_R];
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) acc[r] = (Acc)0;
-        conv8<Acc>(sm + (rb * GT_R) * COL_TW + s, COL_TW, nch, tw, acc);
+        conv8<Acc, COL_TW>(sm + (rb * GT_R) * COL_TW + s, nch, tw, acc);
         if (s0 + s < row_sub) {
 #pragma unroll
             for (int r = 0; r < GT_R; ++r) {
@@ -190,10 +208,20 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
         const int sp = ROW_XT + rnch * GT_R - 1;
         const int in_pitch = (sp * C) | 1, out_pitch = (ROW_XT * C) | 1;
         const size_t smem = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
-        auto k = row_tiled_kernel<T, Mid, Acc>;
-        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const dim3 grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
-        k<<<grid, GT_THREADS, smem, st>>>(src, mid, w, C, total_rows, rlen / 2, row_shift, rnch, in_pitch, out_pitch, rw);
+#define ROW_GO(CC)                                                                                                       \
+    {                                                                                                                    \
+        auto k = row_tiled_kernel<T, Mid, Acc, CC>;                                                                      \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                      \
+        k<<<grid, GT_THREADS, smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rw);             \
+    }
+        switch (C) {
+            case 1: ROW_GO(1) break;
+            case 2: ROW_GO(2) break;
+            case 3: ROW_GO(3) break;
+            default: ROW_GO(4) break;
+        }
+#undef ROW_GO
     }
     {
         const uint32_t row_sub = w * (uint32_t)C;
