@@ -111,7 +111,7 @@ box_v_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, uint32_t
 #pragma unroll
             for (int j = 0; j < N; ++j) sum[j] += v[j] * (S)nhi; }
     }
-    for (int y = y0; y < y1; ++y) {
+    auto emit = [&](int y) {
         T o[N];
 #pragma unroll
         for (int j = 0; j < N; ++j) o[j] = Box<T>::store(sum[j], g);
@@ -126,11 +126,27 @@ box_v_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, uint32_t
 #pragma unroll
             for (int j = 0; j < N; ++j) if (j < n) q[j] = o[j];
         }
+    };
+    constexpr int U = 4;  // rows per iteration: 2*U independent loads in flight per thread
+    int y = y0;
+    for (; y + U <= y1; y += U) {
+        S a[U][N], b[U][N];
+#pragma unroll
+        for (int k = 0; k < U; ++k) { load(min(y + k + r + 1, hmax), a[k]); load(max(y + k - r, 0), b[k]); }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            emit(y + k);
+#pragma unroll
+            for (int j = 0; j < N; ++j) sum[j] = sum[j] + a[k][j] - b[k][j];  // the reference's order: add, then subtract
+        }
+    }
+    for (; y < y1; ++y) {
+        emit(y);
         S a[N], b[N];
         load(min(y + r + 1, hmax), a);
         load(max(y - r, 0), b);
 #pragma unroll
-        for (int j = 0; j < N; ++j) sum[j] = sum[j] + a[j] - b[j];  // the reference's order: add, then subtract
+        for (int j = 0; j < N; ++j) sum[j] = sum[j] + a[j] - b[j];
     }
 }
 
@@ -139,13 +155,33 @@ constexpr int H_ROWS = 32;  // rows per CTA tile = lanes
 constexpr int H_XT = 256;   // output pixels per CTA tile
 constexpr int H_XC = 64;    // pixels per thread chunk
 
+// Copies `n` elements between a global row and a shared row that share the same 4-byte phase:
+// scalar head up to the first word boundary, 32-bit body, scalar tail.  No over-read.  (Words,
+// not uint4: shared rows must keep an odd word pitch for the lane-per-row passes, so they are
+// only word aligned.)
+template <typename T, bool TO_SHARED>
+__device__ __forceinline__ void copy_row_phased(const T *from, T *to, int n, int lane) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(TO_SHARED ? (const void *)from : (const void *)to);  // the global side
+    constexpr int PER = 4 / sizeof(T);
+    int head = (int)(((4 - (a & 3)) & 3) / sizeof(T));
+    if (head > n) head = n;
+    const int body = (n - head) / PER;
+    if (lane < head) to[lane] = from[lane];
+    const uint32_t *vs = reinterpret_cast<const uint32_t *>(from + head);
+    uint32_t *vd = reinterpret_cast<uint32_t *>(to + head);
+#pragma unroll 4
+    for (int v = lane; v < body; v += 32) vd[v] = vs[v];
+    const int done = head + body * PER;
+    if (lane < n - done) to[done + lane] = from[done + lane];
+}
+
 template <typename T, int C>
 __global__ void __launch_bounds__(THREADS)
 box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t total_rows, int in_pitch, int out_pitch) {
     typedef typename Box<T>::sum_t S;
     extern __shared__ __align__(16) unsigned char smem[];
-    T *s_in = reinterpret_cast<T *>(smem);                                    // [H_ROWS][in_pitch]   (pitch in elements)
-    T *s_out = reinterpret_cast<T *>(smem) + (size_t)H_ROWS * in_pitch;        // [H_ROWS][out_pitch]
+    T *s_in = reinterpret_cast<T *>(smem);                              // [H_ROWS][in_pitch]   (pitch in elements; odd number of words)
+    T *s_out = reinterpret_cast<T *>(smem) + (size_t)H_ROWS * in_pitch;  // [H_ROWS][out_pitch]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int x0 = blockIdx.x * H_XT;
     const size_t row0 = (size_t)blockIdx.y * H_ROWS;
@@ -155,12 +191,21 @@ box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t t
     const size_t g_pitch = (size_t)W * C;
     const bool interior = x0 - r >= 0 && x0 + tw + r <= W;
 
+    // a staged row starts at the same 4-byte phase as its global source, so the copy moves whole words
+    auto in_phase = [&](size_t row) -> int {
+        if (!interior) return 0;
+        return (int)((reinterpret_cast<uintptr_t>(src + row * g_pitch + (size_t)(x0 - r) * C) & 3) / sizeof(T));
+    };
+    auto out_phase = [&](size_t row) -> int {
+        return (int)((reinterpret_cast<uintptr_t>(dst + row * g_pitch + (size_t)x0 * C) & 3) / sizeof(T));
+    };
+
     for (int rr = warp; rr < H_ROWS; rr += THREADS / 32) {
-        const T *grow = src + min(row0 + rr, total_rows - 1) * g_pitch;
-        T *s = s_in + (size_t)rr * in_pitch;
+        const size_t row = min(row0 + rr, total_rows - 1);
+        const T *grow = src + row * g_pitch;
+        T *s = s_in + (size_t)rr * in_pitch + in_phase(row);
         if (interior) {
-            const T *q = grow + (size_t)(x0 - r) * C;
-            for (int e = lane; e < sp * C; e += 32) s[e] = q[e];
+            copy_row_phased<T, true>(grow + (size_t)(x0 - r) * C, s, sp * C, lane);
         } else {
             for (int e = lane; e < sp * C; e += 32) {
                 const int p = e / C, c = e - p * C;
@@ -171,13 +216,17 @@ box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t t
     __syncthreads();
 
     const int chunks = (tw + H_XC - 1) / H_XC;
+    const size_t my_row = min(row0 + lane, total_rows - 1);
+    const T *in_row = s_in + (size_t)lane * in_pitch + in_phase(my_row);
+    T *out_row = s_out + (size_t)lane * out_pitch + out_phase(my_row);
     for (int item = warp; item < chunks * C; item += THREADS / 32) {
         const int ck = item / C, c = item - ck * C;
         const int xa = ck * H_XC, xb = min(xa + H_XC, tw);  // outputs [xa, xb) of this tile
-        const T *in = s_in + (size_t)lane * in_pitch + c;    // staged pixel j <-> source pixel x0 - r + j
-        T *out = s_out + (size_t)lane * out_pitch + c;
+        const T *in = in_row + c;                            // staged pixel j <-> source pixel x0 - r + j
+        T *out = out_row + c;
         S sum = (S)0;
         for (int j = xa; j <= xa + 2 * r; ++j) sum += Box<T>::lift(in[j * C]);  // window of output xa
+#pragma unroll 4
         for (int x = xa; x < xb; ++x) {
             out[x * C] = Box<T>::store(sum, g);
             sum = sum + Box<T>::lift(in[(x + 2 * r + 1) * C]) - Box<T>::lift(in[x * C]);
@@ -188,9 +237,7 @@ box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t t
     for (int rr = warp; rr < H_ROWS; rr += THREADS / 32) {
         const size_t row = row0 + rr;
         if (row >= total_rows) break;
-        T *q = dst + row * g_pitch + (size_t)x0 * C;
-        const T *s = s_out + (size_t)rr * out_pitch;
-        for (int e = lane; e < tw * C; e += 32) q[e] = s[e];
+        copy_row_phased<T, false>(s_out + (size_t)rr * out_pitch + out_phase(row), dst + row * g_pitch + (size_t)x0 * C, tw * C, lane);
     }
 }
 
@@ -216,9 +263,10 @@ box_h_direct_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, s
     }
 }
 
-// pitch (in elements of T) >= n with an odd number of 32-bit words per row
-int odd_word_pitch(int n, int tsize) {
-    int words = (n * tsize + 3) / 4;
+// Row pitch (in elements of T) for a staged row of n elements: room for a 4-byte phase shift,
+// whole words, and an odd number of them so the 32 lanes (one row each) hit 32 different banks.
+int staged_pitch(int n, int tsize) {
+    int words = (n * tsize + 3 + 3) / 4;
     words |= 1;
     return words * 4 / tsize;
 }
@@ -238,8 +286,8 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
         g.inv = 1.0f / (float)g.ks;
         {
             // one staged element past the last window keeps the sliding update branch-free
-            const int in_pitch = odd_word_pitch((H_XT + 2 * (int)g.r + 1) * C, sizeof(T));
-            const int out_pitch = odd_word_pitch(H_XT * C, sizeof(T));
+            const int in_pitch = staged_pitch((H_XT + 2 * (int)g.r + 1) * C, sizeof(T));
+            const int out_pitch = staged_pitch(H_XT * C, sizeof(T));
             const size_t smem = (size_t)H_ROWS * (in_pitch + out_pitch) * sizeof(T);
             const dim3 grid((w + H_XT - 1) / H_XT, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
             if (smem > ctx->smem_optin) {

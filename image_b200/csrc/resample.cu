@@ -43,54 +43,68 @@ struct ResizeArgs {
     int tmp_pitch;              // floats per intermediate row
 };
 
-template <typename T> struct Word;  // 32-bit word of subpixels
+// ---- packed f32x2 arithmetic (sm_100+: FFMA2 / FADD2).  Same FLOP rate as the scalar forms
+// but half the issue slots, which is what these issue-bound passes are short of. ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+// 32-bit word of subpixels -> floats.  Integer subpixels are converted with the 2^23 trick
+// (PRMT builds the float 8388608 + v, one FADD removes the bias: exact) because I2F issues on
+// the quarter-rate XU pipe (measured 15 lanes/clk/SM vs > 34 for PRMT + FADD), which made the
+// vertical pass XU-bound in the first profile.
+template <typename T> struct Word;
 template <> struct Word<uint8_t> {
     static constexpr int N = 4;
-    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[4]) {
-        f[0] = (float)(w & 0xffu); f[1] = (float)((w >> 8) & 0xffu);
-        f[2] = (float)((w >> 16) & 0xffu); f[3] = (float)(w >> 24);
+    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[4]) {  // 2^23 + v
+        f[0] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540));
+        f[1] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7541));
+        f[2] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7542));
+        f[3] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7543));
     }
 };
 template <> struct Word<uint16_t> {
     static constexpr int N = 2;
-    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[2]) {
-        f[0] = (float)(w & 0xffffu); f[1] = (float)(w >> 16);
+    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[2]) {
+        f[0] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7510));
+        f[1] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7532));
     }
 };
 template <> struct Word<float> {
     static constexpr int N = 1;
-    static __device__ __forceinline__ void unpack(uint32_t w, float (&f)[1]) { f[0] = __uint_as_float(w); }
+    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[1]) { f[0] = __uint_as_float(w); }
 };
+template <typename T> __device__ __forceinline__ float unbias(float m) { return m - 8388608.0f; }
+template <> __device__ __forceinline__ float unbias<float>(float m) { return m; }
 
-// cooperative 2-D copy global -> shared in units of U bytes
-template <typename U>
-__device__ __forceinline__ void stage_rows(const unsigned char *g, size_t g_pitch, unsigned char *s, int s_pitch,
-                                           int rows, int row_bytes, int tid) {
-    const int per_row = row_bytes / (int)sizeof(U);
-    for (int i = tid; i < rows * per_row; i += THREADS) {
-        const int r = i / per_row, v = i - r * per_row;
-        reinterpret_cast<U *>(s + (size_t)r * s_pitch)[v] = __ldg(reinterpret_cast<const U *>(g + (size_t)r * g_pitch) + v);
-    }
+__device__ __forceinline__ void cp_async(void *smem_dst, const void *gsrc, int bytes) {
+    const uint32_t d = smem_u32(smem_dst);
+    if (bytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+    else if (bytes == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(d), "l"(gsrc) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gsrc) : "memory");
 }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// One CTA = one TW x TH tile of the destination of one image (grid: x = tile column, y = tile
+// row, z = image).
 template <typename T, int C, bool STRICT>
 __global__ void __launch_bounds__(THREADS)
 resize_kernel(const ResizeArgs a) {
-    extern __shared__ __align__(16) unsigned char smem[];
-    // layout: [src region | reused as output staging] [tmp f32] [vw tile] [hw tile (transposed)] [hleft tile]
+    extern __shared__ __align__(128) unsigned char smem[];
+    // layout: [src region | reused as output staging] [tmp f32] [vw pairs] [hw pairs (transposed)] [hleft] [mbarrier]
     const int src_bytes = a.max_rows * a.src_pitch;
     unsigned char *s_src = smem;
     float *s_tmp = reinterpret_cast<float *>(smem + src_bytes);
-    float *s_vw = s_tmp + (size_t)a.TH * a.tmp_pitch;
-    float *s_hw = s_vw + a.TH * a.vstride;
+    float2 *s_vw = reinterpret_cast<float2 *>(s_tmp + (size_t)a.TH * a.tmp_pitch);  // [TH][vstride] (w, w)
+    float2 *s_hw = s_vw + a.TH * a.vstride;                                          // [hstride][TW] (w, w)
     int *s_hl = reinterpret_cast<int *>(s_hw + a.TW * a.hstride);
+    __shared__ __align__(8) uint64_t bar;
 
     const int tid = threadIdx.x;
-    const unsigned tiles_per_img = (unsigned)a.tiles_x * a.tiles_y;
-    const unsigned img = blockIdx.x / tiles_per_img;
-    const unsigned trem = blockIdx.x % tiles_per_img;
-    const int ty = trem / a.tiles_x, tx = trem % a.tiles_x;
-
+    const unsigned img = blockIdx.z;
+    const int tx = blockIdx.x, ty = blockIdx.y;
     const int ox0 = tx * a.TW, oy0 = a.dst_row0 + ty * a.TH;
     const int tw = min(a.TW, (int)a.nw - ox0);
     const int th = min(a.TH, (int)(a.dst_row0 + a.dst_rows) - oy0);
@@ -99,62 +113,117 @@ resize_kernel(const ResizeArgs a) {
     const int col1 = a.hleft[ox0 + tw - 1] + a.hcount[ox0 + tw - 1];
     const int row0 = a.vleft[oy0];
     const int row1 = a.vleft[oy0 + th - 1] + a.vcount[oy0 + th - 1];
-    const int cols = col1 - col0, rows = row1 - row0;
-    const int row_sub = cols * C;  // subpixels per staged row
+    const int rows = row1 - row0;
 
     const T *src = reinterpret_cast<const T *>(reinterpret_cast<const unsigned char *>(a.src) + (size_t)img * a.src_img_stride);
     T *dst = reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(a.dst) + (size_t)img * a.dst_img_stride);
 
-    // ---- stage weights ----
-    for (int i = tid; i < th * a.vstride; i += THREADS) s_vw[i] = a.vw[(size_t)oy0 * a.vstride + i];
-    for (int i = tid; i < tw * a.hstride; i += THREADS) {
-        const int oxl = i / a.hstride, k = i % a.hstride;
-        s_hw[k * a.TW + oxl] = a.hw[(size_t)(ox0 + oxl) * a.hstride + k];
-    }
-    for (int i = tid; i < tw; i += THREADS) s_hl[i] = a.hleft[ox0 + i] - col0;
+    // ---- the source region in bytes: rows [row0,row1) x bytes [b0,b1) of each row.  When the
+    // image rows are 16-byte aligned the span is widened to 16-byte boundaries so that every row
+    // is one TMA bulk copy. ----
+    const size_t gp = sizeof(T) * (size_t)a.w * C;  // global row pitch, bytes
+    const unsigned char *gimg = reinterpret_cast<const unsigned char *>(src) + (size_t)(row0 - (int)a.src_row0) * gp;
+    int b0 = col0 * C * (int)sizeof(T), b1 = col1 * C * (int)sizeof(T);
+    const bool rows16 = (gp % 16 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+    if (rows16) { b0 &= ~15; b1 = (b1 + 15) & ~15; }   // b1 <= gp because gp is a multiple of 16
+    const int row_bytes = b1 - b0;
+    const int sub0 = b0 / (int)sizeof(T);               // first staged subpixel of each row
+    const int row_sub = row_bytes / (int)sizeof(T);      // staged subpixels per row
 
-    // ---- stage the source region: rows [row0,row1) x cols [col0,col1) ----
-    {
-        const size_t g_pitch = (size_t)a.w * C;  // subpixels
-        const T *g0 = src + (size_t)(row0 - (int)a.src_row0) * g_pitch + (size_t)col0 * C;
+    if (rows16) {
+        if (tid == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+        __syncthreads();
+        if (tid == 0) mbar_expect_tx(&bar, (uint32_t)(rows * row_bytes));
+        __syncthreads();
+        for (int r = tid; r < rows; r += THREADS)
+            bulk_g2s(s_src + (size_t)r * a.src_pitch, gimg + (size_t)r * gp + b0, (uint32_t)row_bytes, &bar);
+    } else {
         // widest power-of-two unit that divides the row start, the row pitch and the row length
-        const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(g0) | (sizeof(T) * g_pitch) | (sizeof(T) * row_sub) | 16u);
-        const int unit = (int)(mis & (~mis + 1u));  // lowest set bit: 1, 2, 4, 8 or 16 bytes
-        const unsigned char *gb = reinterpret_cast<const unsigned char *>(g0);
-        const size_t gp = sizeof(T) * g_pitch;
-        const int row_bytes = (int)(sizeof(T) * row_sub);
-        if (unit == 16) stage_rows<uint4>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
-        else if (unit == 8) stage_rows<uint2>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
-        else if (unit == 4) stage_rows<uint32_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
-        else if (unit == 2) stage_rows<uint16_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
-        else stage_rows<uint8_t>(gb, gp, s_src, a.src_pitch, rows, row_bytes, tid);
+        const unsigned mis = (unsigned)(reinterpret_cast<uintptr_t>(gimg + b0) | gp | (unsigned)row_bytes | 16u);
+        const int unit = (int)(mis & (~mis + 1u));
+        const int lane = tid & 31;
+        if (unit >= 4) {
+            const int per_row = row_bytes / unit;
+            for (int r = tid >> 5; r < rows; r += THREADS / 32)
+                for (int v = lane; v < per_row; v += 32)
+                    cp_async(s_src + (size_t)r * a.src_pitch + v * unit, gimg + (size_t)r * gp + b0 + v * unit, unit);
+        } else if (unit == 2) {
+            for (int r = tid >> 5; r < rows; r += THREADS / 32) {
+                const uint16_t *g = reinterpret_cast<const uint16_t *>(gimg + (size_t)r * gp + b0);
+                uint16_t *sr = reinterpret_cast<uint16_t *>(s_src + (size_t)r * a.src_pitch);
+#pragma unroll 4
+                for (int v = lane; v < row_bytes / 2; v += 32) sr[v] = __ldg(g + v);
+            }
+        } else {
+            for (int r = tid >> 5; r < rows; r += THREADS / 32) {
+                const unsigned char *g = gimg + (size_t)r * gp + b0;
+                unsigned char *sr = s_src + (size_t)r * a.src_pitch;
+#pragma unroll 4
+                for (int v = lane; v < row_bytes; v += 32) sr[v] = __ldg(g + v);
+            }
+        }
     }
+
+    // ---- stage weights while the copies fly ----
+    for (int i = tid; i < th * a.vstride; i += THREADS) { const float w = a.vw[(size_t)oy0 * a.vstride + i]; s_vw[i] = make_float2(w, w); }
+    for (int i = tid; i < tw * a.hstride; i += THREADS) {
+        const int oxl = i / a.hstride, k = i - oxl * a.hstride;
+        const float w = a.hw[(size_t)(ox0 + oxl) * a.hstride + k];
+        s_hw[k * a.TW + oxl] = make_float2(w, w);
+    }
+    for (int i = tid; i < tw; i += THREADS) s_hl[i] = a.hleft[ox0 + i] * C - sub0;  // subpixel offset into a tmp row
+
+    if (rows16) mbar_wait(&bar, 0);
+    else cp_async_wait_all();
     __syncthreads();
 
     // ---- vertical pass: s_tmp[oyl][s] = acc_init + sum_i src[vleft+i][s] * vw[i] ----
     {
         constexpr int N = Word<T>::N;
         const int words = (row_sub + N - 1) / N;
+        const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
         for (int idx = tid; idx < th * words; idx += THREADS) {
-            const int oyl = idx / words, wd = idx % words;
+            const int oyl = idx / words, wd = idx - oyl * words;
             const int l = a.vleft[oy0 + oyl] - row0, n = a.vcount[oy0 + oyl];
-            const float *wv = s_vw + oyl * a.vstride;
-            float acc[N];
-#pragma unroll
-            for (int j = 0; j < N; ++j) acc[j] = a.acc_init;
+            const float2 *wv = s_vw + oyl * a.vstride;
             const unsigned char *p = s_src + (size_t)l * a.src_pitch + wd * 4;
-            for (int i = 0; i < n; ++i) {
-                float f[N];
-                Word<T>::unpack(*reinterpret_cast<const uint32_t *>(p), f);
-                const float wgt = wv[i];
-#pragma unroll
-                for (int j = 0; j < N; ++j) acc[j] = mac<STRICT>(acc[j], f[j], wgt);
-                p += a.src_pitch;
-            }
             float *t = s_tmp + (size_t)oyl * a.tmp_pitch + wd * N;
-            if (N == 4) *reinterpret_cast<float4 *>(t) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-            else if (N == 2) *reinterpret_cast<float2 *>(t) = make_float2(acc[0], acc[1]);
-            else t[0] = acc[0];
+            if constexpr (!STRICT && N == 4) {
+                f32x2 a01 = pack2(a.acc_init, a.acc_init), a23 = a01;
+                for (int i = 0; i < n; ++i) {
+                    float f[4];
+                    Word<T>::biased(*reinterpret_cast<const uint32_t *>(p), f);
+                    const f32x2 ww = *reinterpret_cast<const f32x2 *>(wv + i);
+                    a01 = fma2(add2(pack2(f[0], f[1]), bias2), ww, a01);
+                    a23 = fma2(add2(pack2(f[2], f[3]), bias2), ww, a23);
+                    p += a.src_pitch;
+                }
+                *reinterpret_cast<ulonglong2 *>(t) = make_ulonglong2(a01, a23);
+            } else if constexpr (!STRICT && N == 2) {
+                f32x2 a01 = pack2(a.acc_init, a.acc_init);
+                for (int i = 0; i < n; ++i) {
+                    float f[2];
+                    Word<T>::biased(*reinterpret_cast<const uint32_t *>(p), f);
+                    a01 = fma2(add2(pack2(f[0], f[1]), bias2), *reinterpret_cast<const f32x2 *>(wv + i), a01);
+                    p += a.src_pitch;
+                }
+                *reinterpret_cast<f32x2 *>(t) = a01;
+            } else {
+                float acc[N];
+#pragma unroll
+                for (int j = 0; j < N; ++j) acc[j] = a.acc_init;
+                for (int i = 0; i < n; ++i) {
+                    float f[N];
+                    Word<T>::biased(*reinterpret_cast<const uint32_t *>(p), f);
+                    const float wgt = wv[i].x;
+#pragma unroll
+                    for (int j = 0; j < N; ++j) acc[j] = mac<STRICT>(acc[j], unbias<T>(f[j]), wgt);
+                    p += a.src_pitch;
+                }
+                if (N == 4) *reinterpret_cast<float4 *>(t) = make_float4(acc[0], acc[1 % N], acc[2 % N], acc[3 % N]);
+                else if (N == 2) *reinterpret_cast<float2 *>(t) = make_float2(acc[0], acc[1 % N]);
+                else t[0] = acc[0];
+            }
         }
     }
     __syncthreads();
@@ -169,23 +238,36 @@ resize_kernel(const ResizeArgs a) {
             const int oxl = (e >> 3) % a.TW;
             if (oyl >= th || oxl >= tw) continue;
             const int n = a.hcount[ox0 + oxl];
-            const float *t = s_tmp + (size_t)oyl * a.tmp_pitch + s_hl[oxl] * C;
-            const float *wh = s_hw + oxl;
+            const float *t = s_tmp + (size_t)oyl * a.tmp_pitch + s_hl[oxl];
+            const float2 *wh = s_hw + oxl;
             float acc[C];
-#pragma unroll
-            for (int c = 0; c < C; ++c) acc[c] = 0.0f;
-            for (int i = 0; i < n; ++i) {
-                const float wgt = wh[i * a.TW];
-                float v[C];
-                if (C == 4) { const float4 q = *reinterpret_cast<const float4 *>(t); v[0] = q.x; v[1] = q.y; v[2 % C] = q.z; v[3 % C] = q.w; }
-                else if (C == 2) { const float2 q = *reinterpret_cast<const float2 *>(t); v[0] = q.x; v[1 % C] = q.y; }
-                else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c) v[c] = t[c];
+            if constexpr (!STRICT && C == 4) {
+                f32x2 a01 = 0ull, a23 = 0ull;  // (+0.0f, +0.0f)
+                for (int i = 0; i < n; ++i) {
+                    const ulonglong2 q = *reinterpret_cast<const ulonglong2 *>(t);
+                    const f32x2 ww = *reinterpret_cast<const f32x2 *>(wh + i * a.TW);
+                    a01 = fma2(q.x, ww, a01);
+                    a23 = fma2(q.y, ww, a23);
+                    t += 4;
                 }
+                unpack2(a01, acc[0], acc[1 % C]);
+                unpack2(a23, acc[2 % C], acc[3 % C]);
+            } else {
 #pragma unroll
-                for (int c = 0; c < C; ++c) acc[c] = mac<STRICT>(acc[c], v[c], wgt);
-                t += C;
+                for (int c = 0; c < C; ++c) acc[c] = 0.0f;
+                for (int i = 0; i < n; ++i) {
+                    const float wgt = wh[i * a.TW].x;
+                    float v[C];
+                    if (C == 4) { const float4 q = *reinterpret_cast<const float4 *>(t); v[0] = q.x; v[1 % C] = q.y; v[2 % C] = q.z; v[3 % C] = q.w; }
+                    else if (C == 2) { const float2 q = *reinterpret_cast<const float2 *>(t); v[0] = q.x; v[1 % C] = q.y; }
+                    else {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) v[c] = t[c];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; ++c) acc[c] = mac<STRICT>(acc[c], v[c], wgt);
+                    t += C;
+                }
             }
             T *o = s_out + (size_t)oyl * out_pitch + oxl * C;
 #pragma unroll
@@ -201,18 +283,15 @@ resize_kernel(const ResizeArgs a) {
         const int sub = tw * C;
         const bool vec_ok = (sizeof(T) * d_pitch) % 16 == 0 && (reinterpret_cast<uintptr_t>(g0) & 15) == 0 &&
                             (sizeof(T) * sub) % 16 == 0 && (sizeof(T) * out_pitch) % 16 == 0;
+        const int lane = tid & 31;
         if (vec_ok) {
             const int v_per_row = (int)(sizeof(T) * sub / 16);
-            for (int i = tid; i < th * v_per_row; i += THREADS) {
-                const int r = i / v_per_row, v = i % v_per_row;
-                reinterpret_cast<uint4 *>(g0 + (size_t)r * d_pitch)[v] =
-                    reinterpret_cast<const uint4 *>(s_out + (size_t)r * out_pitch)[v];
-            }
+            for (int r = tid >> 5; r < th; r += THREADS / 32)
+                for (int v = lane; v < v_per_row; v += 32)
+                    reinterpret_cast<uint4 *>(g0 + (size_t)r * d_pitch)[v] = reinterpret_cast<const uint4 *>(s_out + (size_t)r * out_pitch)[v];
         } else {
-            for (int i = tid; i < th * sub; i += THREADS) {
-                const int r = i / sub, s = i % sub;
-                g0[(size_t)r * d_pitch + s] = s_out[(size_t)r * out_pitch + s];
-            }
+            for (int r = tid >> 5; r < th; r += THREADS / 32)
+                for (int v = lane; v < sub; v += 32) g0[(size_t)r * d_pitch + v] = s_out[(size_t)r * out_pitch + v];
         }
     }
 }
@@ -297,14 +376,15 @@ bool plan_tiles(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             p.max_cols = max_extent(ht, 0, nw, TW);
             p.max_rows = max_extent(vt, dst_row0, dst_rows, TH);
             const int out_bytes_row = TW * C * tsize;
-            p.src_pitch = round_up(std::max(p.max_cols * C * tsize, out_bytes_row), 16);
-            int tp = round_up(p.max_cols * C, 4);
+            // +32: the span may be widened to 16-byte boundaries on both sides
+            p.src_pitch = round_up(std::max(p.max_cols * C * tsize + 32, out_bytes_row), 16);
+            int tp = round_up(p.src_pitch / tsize, 4);
             if ((tp / 4) % 2 == 0) tp += 4;  // odd number of 16-byte units: the 8-row lane pattern hits 8 bank groups
             p.tmp_pitch = tp;
             const int src_rows_needed = std::max(p.max_rows, (TH * out_bytes_row + p.src_pitch - 1) / p.src_pitch);
             p.max_rows = src_rows_needed;
-            p.smem = (size_t)p.max_rows * p.src_pitch + (size_t)TH * p.tmp_pitch * 4 + (size_t)TH * vt.stride * 4 +
-                     (size_t)TW * ht.stride * 4 + (size_t)TW * 4;
+            p.smem = (size_t)p.max_rows * p.src_pitch + (size_t)TH * p.tmp_pitch * 4 + (size_t)TH * vt.stride * 8 +
+                     (size_t)TW * ht.stride * 8 + (size_t)TW * 4 + 128;
             if (p.smem > smem_budget) continue;
             // cost: staged bytes + intermediate work per destination pixel, with a mild
             // penalty for tiles so large that few CTAs fit per SM
@@ -319,7 +399,7 @@ bool plan_tiles(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
 }
 
 template <typename T, int C>
-int launch_tc(const ResizeArgs &a, size_t smem, unsigned grid, bool strict, cudaStream_t st) {
+int launch_tc(const ResizeArgs &a, size_t smem, dim3 grid, bool strict, cudaStream_t st) {
     auto k = strict ? resize_kernel<T, C, true> : resize_kernel<T, C, false>;
     if (smem > 48 * 1024) B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, THREADS, smem, st>>>(a);
@@ -328,7 +408,7 @@ int launch_tc(const ResizeArgs &a, size_t smem, unsigned grid, bool strict, cuda
 }
 
 template <typename T>
-int launch_t(const ResizeArgs &a, size_t smem, unsigned grid, bool strict, cudaStream_t st) {
+int launch_t(const ResizeArgs &a, size_t smem, dim3 grid, bool strict, cudaStream_t st) {
     switch (a.C) {
         case 1: return launch_tc<T, 1>(a, smem, grid, strict, st);
         case 2: return launch_tc<T, 2>(a, smem, grid, strict, st);
@@ -487,12 +567,12 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     a.tiles_x = (int)((nw + p.TW - 1) / p.TW);
     a.tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
     a.max_cols = p.max_cols; a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.tmp_pitch = p.tmp_pitch;
-    const uint64_t grid = (uint64_t)a.tiles_x * a.tiles_y * n_images;
-    if (grid > 0x7fffffffull) return fail(B200IMG_ERR_DIMENSION, "resize: too many tiles for one launch");
+    if (a.tiles_y > 65535 || n_images > 65535) return fail(B200IMG_ERR_DIMENSION, "resize: too many tiles / images for one launch");
+    const dim3 grid((unsigned)a.tiles_x, (unsigned)a.tiles_y, n_images);
     switch (dtype) {
-        case B200IMG_U8: return launch_t<uint8_t>(a, p.smem, (unsigned)grid, strict, st);
-        case B200IMG_U16: return launch_t<uint16_t>(a, p.smem, (unsigned)grid, strict, st);
-        default: return launch_t<float>(a, p.smem, (unsigned)grid, strict, st);
+        case B200IMG_U8: return launch_t<uint8_t>(a, p.smem, grid, strict, st);
+        case B200IMG_U16: return launch_t<uint16_t>(a, p.smem, grid, strict, st);
+        default: return launch_t<float>(a, p.smem, grid, strict, st);
     }
 }
 
