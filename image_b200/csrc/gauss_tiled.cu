@@ -19,6 +19,8 @@
 // applied while staging.
 #include "common.cuh"
 
+#include <type_traits>
+
 namespace b200 {
 
 constexpr int GT_R = 8;           // outputs per thread along the filter axis
@@ -78,6 +80,72 @@ __device__ __forceinline__ void conv8(const uint32_t *in, int nch, const TapWeig
         }
 #pragma unroll
         for (int i = 0; i < GT_R - 1; ++i) win[i] = win[GT_R + i];
+    }
+}
+
+// ---- packed f32x2 variant (FFMA2): two independent convolutions per thread.  FFMA2 has the
+// FLOP rate of FFMA (measured 126 vs 123 lanes/clk/SM) at half the issue slots, so the loads,
+// constant fetches and loop overhead of the loop body fit beside a saturated FMA pipe. ----
+typedef unsigned long long f32x2;
+struct TapWeights2 { f32x2 w[GT_MAX_TAPS]; };  // (w, w) pairs, zero padded
+__device__ __forceinline__ f32x2 pack2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+
+// acc[r] = (sum_k A[(r+k)*STRIDE] w[k], sum_k B[(r+k)*STRIDE] w[k]).  PAIRED: B = A + 1 and A is
+// 8-byte aligned, so one LDS.64 fetches both.
+template <int STRIDE, bool PAIRED>
+__device__ __forceinline__ void conv8x2(const float *inA, const float *inB, int nch, const TapWeights2 &tw, f32x2 (&acc)[GT_R]) {
+    f32x2 win[2 * GT_R - 1];
+    auto ld = [&](int i) -> f32x2 {
+        if constexpr (PAIRED) return *reinterpret_cast<const f32x2 *>(inA + i * STRIDE);
+        else return pack2(inA[i * STRIDE], inB[i * STRIDE]);
+    };
+#pragma unroll
+    for (int i = 0; i < GT_R - 1; ++i) win[i] = ld(i);
+    inA += (GT_R - 1) * STRIDE;
+    inB += (GT_R - 1) * STRIDE;
+#pragma unroll 1
+    for (int ch = 0; ch < nch; ++ch) {
+#pragma unroll
+        for (int i = 0; i < GT_R; ++i) win[GT_R - 1 + i] = ld(i);
+        inA += GT_R * STRIDE;
+        inB += GT_R * STRIDE;
+#pragma unroll
+        for (int kk = 0; kk < GT_R; ++kk) {
+            const f32x2 wk = tw.w[ch * GT_R + kk];
+#pragma unroll
+            for (int r = 0; r < GT_R; ++r) acc[r] = fma2(win[r + kk], wk, acc[r]);
+        }
+#pragma unroll
+        for (int i = 0; i < GT_R - 1; ++i) win[i] = win[GT_R + i];
+    }
+}
+
+// u8 / u16 / f32 source subpixels of a row -> f32 words in shared memory.  Integer types go a
+// 32-bit word at a time through the 2^23 trick (I2F would run on the quarter-rate XU pipe).
+// `s` receives elements [0, n) of `g`; needs g's row pitch and base 4-byte aligned (checked by the caller).
+template <typename In>
+__device__ __forceinline__ void stage_convert_row(const In *g, float *s, int n, int lane) {
+    if constexpr (sizeof(In) == 4) {
+        for (int e = lane; e < n; e += 32) s[e] = g[e];
+    } else {
+        constexpr int PER = 4 / sizeof(In);
+        const int phase = (int)((reinterpret_cast<uintptr_t>(g) & 3) / sizeof(In));  // elements before g in its word
+        const uint32_t *gw = reinterpret_cast<const uint32_t *>(g - phase);
+        const int words = (phase + n + PER - 1) / PER;
+        for (int wi = lane; wi < words; wi += 32) {
+            const uint32_t w = __ldg(gw + wi);
+            const int e0 = wi * PER - phase;
+#pragma unroll
+            for (int j = 0; j < PER; ++j) {
+                const int e = e0 + j;
+                uint32_t m;
+                if constexpr (PER == 4) m = __byte_perm(w, 0x4B000000u, 0x7540 + j);
+                else m = __byte_perm(w, 0x4B000000u, j == 0 ? 0x7510 : 0x7532);
+                if (e >= 0 && e < n) s[e] = __uint_as_float(m) - 8388608.0f;
+            }
+        }
     }
 }
 
@@ -192,6 +260,124 @@ col_tiled_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
     }
 }
 
+// ---- f32 engine, FFMA2 kernels ------------------------------------------------------------------
+// Row pass: lane = row, warp item = (pixel blocks xb and xb + 4, channel): 16 outputs per thread.
+template <typename In, int C>
+__global__ void __launch_bounds__(GT_THREADS)
+row_f32x2_kernel(const In *__restrict__ src, float *__restrict__ mid, uint32_t W, size_t total_rows, int half,
+                 int shift, int nch, int in_pitch, const __grid_constant__ TapWeights2 tw) {
+    constexpr int OUT_PITCH = (ROW_XT * C) | 1;
+    extern __shared__ __align__(16) uint32_t sm[];
+    float *s_in = reinterpret_cast<float *>(sm);          // [ROW_ROWS][in_pitch]
+    float *s_out = s_in + (size_t)ROW_ROWS * in_pitch;    // [ROW_ROWS][OUT_PITCH]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int x0 = blockIdx.x * ROW_XT;
+    const size_t row0 = (size_t)blockIdx.y * ROW_ROWS;
+    const int sp = ROW_XT + nch * GT_R - 1;
+    const int row_elems = sp * C;
+    const size_t g_pitch = (size_t)W * C;
+    const int xs = x0 - half - shift;
+    const bool interior = xs >= 0 && xs + sp <= (int)W;
+    const bool words_ok = (g_pitch * sizeof(In)) % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
+
+    for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
+        const In *g = src + min(row0 + r, total_rows - 1) * g_pitch;
+        float *s = s_in + r * in_pitch;
+        if (interior && words_ok) {
+            stage_convert_row<In>(g + (size_t)xs * C, s, row_elems, lane);
+        } else {
+            for (int e = lane; e < row_elems; e += 32) {
+                const int p = e / C, c = e - p * C;
+                const int px = min(max(xs + p, 0), (int)W - 1);
+                s[e] = (float)g[(size_t)px * C + c];
+            }
+        }
+    }
+    __syncthreads();
+
+    constexpr int HALF_BLOCKS = ROW_XT / GT_R / 2;  // 4: item pairs block xb with block xb + 4
+    for (int item = warp; item < HALF_BLOCKS * C; item += GT_THREADS / 32) {
+        const int xb = item / C, c = item - xb * C;
+        f32x2 acc[GT_R];
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) acc[r] = 0ull;
+        const float *a = s_in + lane * in_pitch + (xb * GT_R) * C + c;
+        conv8x2<C, false>(a, a + HALF_BLOCKS * GT_R * C, nch, tw, acc);
+        float *o = s_out + lane * OUT_PITCH + (xb * GT_R) * C + c;
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) unpack2(acc[r], o[r * C], o[(HALF_BLOCKS * GT_R + r) * C]);
+    }
+    __syncthreads();
+
+    const int out_elems = min(ROW_XT, (int)W - x0) * C;
+    for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
+        const size_t row = row0 + r;
+        if (row >= total_rows) break;
+        float *g = mid + row * g_pitch + (size_t)x0 * C;
+        const float *s = s_out + r * OUT_PITCH;
+#pragma unroll 4
+        for (int e = lane; e < out_elems; e += 32) g[e] = s[e];
+    }
+}
+
+// Column pass: thread = two adjacent subpixel columns x 8 rows; one LDS.64 per staged row.
+template <typename Out>
+__global__ void __launch_bounds__(GT_THREADS)
+col_f32x2_kernel(const float *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
+                 int nch, int zero_first_row, const __grid_constant__ TapWeights2 tw) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    float *s = reinterpret_cast<float *>(sm);  // [COL_TH + nch*8 - 1][COL_TW]
+    const int tid = threadIdx.x;
+    const uint32_t s0 = blockIdx.x * COL_TW;
+    const uint32_t img = blockIdx.y / tiles_y;
+    const int y0 = (int)(blockIdx.y % tiles_y) * COL_TH;
+    const int sr = COL_TH + nch * GT_R - 1;
+    const float *m = mid + (size_t)img * H * row_sub;
+
+    // stage [sr][COL_TW] with clamped rows; 16-byte async copies when the rows allow it
+    const bool vec = (row_sub % 4 == 0) && (s0 + COL_TW <= row_sub) && ((reinterpret_cast<uintptr_t>(m) & 15) == 0);
+    if (vec) {
+        constexpr int VPR = COL_TW / 4;  // 16-byte vectors per staged row
+        for (int i = tid; i < sr * VPR; i += GT_THREADS) {
+            const int r = i / VPR, v = i - r * VPR;
+            const int y = min(max(y0 - half + r, 0), (int)H - 1);
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(s + r * COL_TW + v * 4);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(m + (size_t)y * row_sub + s0 + v * 4) : "memory");
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
+    } else {
+        const int c = tid % COL_TW;
+        const uint32_t col = min(s0 + c, row_sub - 1);
+        for (int r = tid / COL_TW; r < sr; r += GT_THREADS / COL_TW) {
+            const int y = min(max(y0 - half + r, 0), (int)H - 1);
+            s[r * COL_TW + c] = m[(size_t)y * row_sub + col];
+        }
+    }
+    __syncthreads();
+
+    Out *d = dst + (size_t)img * H * row_sub;
+    for (int item = tid; item < (COL_TW / 2) * (COL_TH / GT_R); item += GT_THREADS) {
+        const int cp = item % (COL_TW / 2), rb = item / (COL_TW / 2);
+        f32x2 acc[GT_R];
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) acc[r] = 0ull;
+        const float *a = s + (rb * GT_R) * COL_TW + 2 * cp;
+        conv8x2<COL_TW, true>(a, a + 1, nch, tw, acc);
+        const uint32_t col = s0 + 2 * cp;
+#pragma unroll
+        for (int r = 0; r < GT_R; ++r) {
+            const int y = y0 + rb * GT_R + r;
+            if (y >= (int)H) break;
+            float v0, v1;
+            unpack2(acc[r], v0, v1);
+            Out *o = d + (size_t)y * row_sub + col;
+            const bool z = zero_first_row && y == 0;
+            if (col < row_sub) o[0] = z ? (Out)0 : St<Out, float>::f(v0);
+            if (col + 1 < row_sub) o[1] = z ? (Out)0 : St<Out, float>::f(v1);
+        }
+    }
+}
+
 }  // namespace
 
 // Launches both passes.  rk / ck are the scanned kernels (f32 bits or Q0.15), lengths odd <= 128.
@@ -199,21 +385,29 @@ template <typename T, typename Mid, typename Acc>
 int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
                     const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
                     cudaStream_t st) {
-    TapWeights rw, cw;
-    for (int i = 0; i < GT_MAX_TAPS; ++i) { rw.w[i] = i < rlen ? rk[i] : 0u; cw.w[i] = i < clen ? ck[i] : 0u; }
     const int rnch = (rlen + GT_R - 1) / GT_R, cnch = (clen + GT_R - 1) / GT_R;
     const size_t total_rows = (size_t)h * n_images;
+    const uint32_t row_sub = w * (uint32_t)C;
+    const int tiles_y = (int)((h + COL_TH - 1) / COL_TH);
+    const int sp = ROW_XT + rnch * GT_R - 1;
+    const int in_pitch = (sp * C + 4) | 1, out_pitch = (ROW_XT * C) | 1;
+    const size_t row_smem = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
+    const size_t col_smem = (size_t)(COL_TH + cnch * GT_R - 1) * COL_TW * 4;
+    const dim3 row_grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
+    const dim3 col_grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
 
-    {
-        const int sp = ROW_XT + rnch * GT_R - 1;
-        const int in_pitch = (sp * C) | 1, out_pitch = (ROW_XT * C) | 1;
-        const size_t smem = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
-        const dim3 grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
-#define ROW_GO(CC)                                                                                                       \
-    {                                                                                                                    \
-        auto k = row_tiled_kernel<T, Mid, Acc, CC>;                                                                      \
-        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));                      \
-        k<<<grid, GT_THREADS, smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rw);             \
+    if constexpr (std::is_same<Acc, float>::value) {
+        TapWeights2 rwl, cwl;
+        for (int i = 0; i < GT_MAX_TAPS; ++i) {
+            const uint32_t a = i < rlen ? rk[i] : 0u, b = i < clen ? ck[i] : 0u;
+            rwl.w[i] = ((f32x2)a << 32) | a;
+            cwl.w[i] = ((f32x2)b << 32) | b;
+        }
+#define ROW_GO(CC)                                                                                                   \
+    {                                                                                                                \
+        auto k = row_f32x2_kernel<T, CC>;                                                                            \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem));              \
+        k<<<row_grid, GT_THREADS, row_smem, st>>>(src, (float *)mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rwl); \
     }
         switch (C) {
             case 1: ROW_GO(1) break;
@@ -222,15 +416,28 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
             default: ROW_GO(4) break;
         }
 #undef ROW_GO
+        auto k = col_f32x2_kernel<T>;
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));
+        k<<<col_grid, GT_THREADS, col_smem, st>>>((const float *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl);
+    } else {
+        TapWeights rw, cw;
+        for (int i = 0; i < GT_MAX_TAPS; ++i) { rw.w[i] = i < rlen ? rk[i] : 0u; cw.w[i] = i < clen ? ck[i] : 0u; }
+#define ROW_GO(CC)                                                                                                   \
+    {                                                                                                                \
+        auto k = row_tiled_kernel<T, Mid, Acc, CC>;                                                                  \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem));              \
+        k<<<row_grid, GT_THREADS, row_smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rw); \
     }
-    {
-        const uint32_t row_sub = w * (uint32_t)C;
-        const int tiles_y = (int)((h + COL_TH - 1) / COL_TH);
-        const size_t smem = (size_t)(COL_TH + cnch * GT_R - 1) * COL_TW * 4;
+        switch (C) {
+            case 1: ROW_GO(1) break;
+            case 2: ROW_GO(2) break;
+            case 3: ROW_GO(3) break;
+            default: ROW_GO(4) break;
+        }
+#undef ROW_GO
         auto k = col_tiled_kernel<Mid, T, Acc>;
-        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        const dim3 grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
-        k<<<grid, GT_THREADS, smem, st>>>(mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cw);
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));
+        k<<<col_grid, GT_THREADS, col_smem, st>>>(mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cw);
     }
     B200_CUDA(cudaGetLastError());
     return B200IMG_OK;
