@@ -24,6 +24,8 @@
 #include "common.cuh"
 #include "host_tables.h"
 
+#include <mutex>
+
 namespace b200 {
 namespace {
 
@@ -347,4 +349,80 @@ int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
     }
 }
 
+
+// ---- b200img_fast_blur_noalloc_dev: the box blur for callers that must not allocate ----------
+//
+// The ordinary entry points take the transient image of the blur (the horizontal pass writes
+// it, the vertical pass reads it) from a cached cudaMalloc'd pool.  Some callers cannot let a
+// library do that: a serving process that has handed the whole GPU to its own memory pool (a
+// cudaMalloc from here would fail or eat into memory it has budgeted), or a latency-critical
+// loop in which cudaMalloc's implicit device synchronisation and driver lock are not acceptable.
+// For them the transient lives in this fixed array instead.  It is part of the library image:
+// every GPU that loads libb200img holds these 32 MiB until the process exits.
+namespace {
+
+constexpr size_t NOALLOC_SCRATCH_BYTES = (size_t)32 << 20;  // fits 3840 x 2160 Rgba8 (31.6 MiB)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address; the
+// address is looked up once per device (with that device current) and remembered here.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+bool g_noalloc_ready[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mu;
+
+int noalloc_scratch_ptr(int dev, void **out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ready[dev]) {
+        void *p = nullptr;
+        B200_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = p;
+        g_noalloc_ready[dev] = true;
+    }
+    *out = g_noalloc_ptr[dev];
+    return B200IMG_OK;
+}
+
+}  // namespace
 }  // namespace b200
+
+extern "C" int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                                              void *d_dst, float sigma, void *stream) {
+    using namespace b200;
+    if (channels < 1 || channels > 4) return fail(B200IMG_ERR_BAD_ARG, "fast_blur_noalloc: channels must be 1..4 (got %d)", channels);
+    if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "fast_blur_noalloc: bad dtype %d", dtype);
+    size_t bytes;
+    if (!checked_mul(w, h, (size_t)channels, dtype_size(dtype), &bytes)) return fail(B200IMG_ERR_DIMENSION, "fast_blur_noalloc: size overflows");
+    if (bytes == 0) return B200IMG_OK;  // empty image: nothing to blur
+    if (bytes > NOALLOC_SCRATCH_BYTES)
+        return fail(B200IMG_ERR_UNSUPPORTED,
+                    "fast_blur_noalloc: the image needs %zu bytes of transient storage but the built-in scratch holds %zu; "
+                    "use b200img_fast_blur_dev (which allocates) for images this large", bytes, NOALLOC_SCRATCH_BYTES);
+    if (!d_src || !d_dst) return fail(B200IMG_ERR_BAD_ARG, "fast_blur_noalloc: null buffer");
+    uint32_t radii[3];
+    boxes_for_gauss(sigma, radii);
+    for (int i = 0; i < 3; ++i)
+        if (radii[i] >= (1u << 23)) return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur_noalloc: box radius %u is beyond the supported range", radii[i]);
+
+    int dev;
+    B200_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur_noalloc: device index %d not supported", dev);
+    // device facts straight from the runtime: the shared per-device context lives on the heap
+    DeviceCtx ctx;
+    int sms = 0, smem = 0, major = 0;
+    B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    B200_CUDA(cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    B200_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major < 10) return fail(B200IMG_ERR_CUDA, "fast_blur_noalloc: device %d is not sm_100", dev);
+    ctx.device = dev; ctx.sm_count = sms; ctx.smem_optin = (size_t)smem;
+
+    void *tmp;
+    int rc = noalloc_scratch_ptr(dev, &tmp);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (dtype) {
+        case B200IMG_U8: return run<uint8_t>(d_src, d_dst, tmp, w, h, channels, 1, radii, &ctx, st);
+        case B200IMG_U16: return run<uint16_t>(d_src, d_dst, tmp, w, h, channels, 1, radii, &ctx, st);
+        default: return run<float>(d_src, d_dst, tmp, w, h, channels, 1, radii, &ctx, st);
+    }
+}

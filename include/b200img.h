@@ -183,6 +183,23 @@ int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int c
                                 int dtype, void *d_dst, uint32_t n_images, float sigma,
                                 void *stream);
 
+/* No counterpart in the reference.  Same result as b200img_fast_blur_dev for one image, but
+ * this entry point allocates nothing: the blur's transient image lives in a fixed 32 MiB
+ * array inside the library (held by every GPU that loads it, until the process exits)
+ * instead of a cudaMalloc'd pool.  It is for callers that cannot let a library allocate --
+ * a serving process whose own pool owns all device memory, or a latency-critical loop that
+ * cannot take cudaMalloc's device-wide synchronisation.  Limits and rules:
+ *   - w * h * channels * sizeof(subpixel) must be <= 33,554,432 bytes (3840x2160 Rgba8
+ *     fits); larger images are refused with B200IMG_ERR_UNSUPPORTED.
+ *   - The first call on each device looks up the array's device address; make that first
+ *     call outside any stream capture.
+ *   - All calls on a device share the one array and it keeps whatever the last call left in
+ *     it (every call overwrites what it reads, nothing needs clearing).  Two calls whose GPU
+ *     work can overlap -- different streams, or different host threads -- race on it: run
+ *     them on one stream or order them yourself. */
+int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                                  void *d_dst, float sigma, void *stream);
+
 /* ---- pixel-format conversions --------------------------------------------
  * mode CAST    = DynamicImage::to_* / into_* (src/images/dynimage.rs:320-568
  *                -> CicpRgb::cast_pixels src/metadata/cicp.rs:706-1033;
