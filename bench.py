@@ -180,6 +180,11 @@ def run_b200(args):
     e2e_val = world * mp_step / e2e_s
     assert np.array_equal(pin_dst.numpy()[::97, ::89], dst[0, ::97, ::89].cpu().numpy()), "e2e and device paths disagree"
 
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):  # dram__bytes_read + write of the step's kernels, from the committed ncu --set full capture
+        traffic = json.load(open(tpath)).get("blur_sigma10_4k_rgb8_batch8", {}).get("dram_bytes_per_step")
+
     out = {
         "metric": "megapixels/sec (Gaussian blur sigma=10, 3840x2160 Rgb8 batch)", "value": round(value, 1),
         "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 4),
@@ -189,10 +194,15 @@ def run_b200(args):
                    "batch_per_gpu": BATCH, "l2": f"inputs larger than L2 ({2 * BATCH * W4K * H4K * 3 / 1e6:.0f} MB per step)",
                    "flags": "FP_FAST (+-1 LSB vs reference)", "checksum": checksum},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s",
-                     "frac": round(achieved / hbm, 4), "traffic": None, "peak_source": hbm_src,
+                     "frac": round(achieved / hbm, 4), "traffic": traffic, "peak_source": hbm_src,
                      "kernel": "gaussian row+column passes of one batch call",
                      "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "65 taps/axis on the FP32 pipes: the op is FMA-issue bound, see DESIGN.md"},
+                     "fp32_bound": {"fma_per_step": 2 * 72 * BATCH * W4K * H4K * 3, "peak_tfma_s": 35.9,
+                                    "frac": round(2 * 72 * BATCH * W4K * H4K * 3 / 35.9e12 / (ms / 1e3), 4),
+                                    "note": "65 taps (72 padded) x 2 passes per subpixel on the FP32 pipes; peak = FFMA rate "
+                                            "measured with tools/micro/ffma2.cu"},
+                     "note": "traffic = both kernels of the call (f32 intermediate written and re-read); the op is "
+                             "FP32-pipe bound, see DESIGN.md section 5"},
         "e2e": {"value": round(e2e_val, 1), "unit": "MP/s", "h2d_bytes_per_step": BATCH * W4K * H4K * 3,
                 "d2h_bytes_per_step": BATCH * W4K * H4K * 3},
         "gpu_launches": args.steps * GAUSS_LAUNCHES,
