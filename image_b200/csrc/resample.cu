@@ -15,12 +15,21 @@
 // dense contraction, so tensor cores are not used.
 #include "common.cuh"
 #include "host_tables.h"
+#include "packed.cuh"
 
 #include <list>
 #include <mutex>
 #include <tuple>
 
 namespace b200 {
+
+// resample_stream.cu: column-streaming kernel for integer-subpixel downscales
+int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
+                      size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t n_images,
+                      const AxisTable &vt, const int32_t *d_vleft, const int32_t *d_vcount, const float *d_vw,
+                      const AxisTable &ht, const int32_t *d_hleft, const int32_t *d_hcount, const float *d_hw,
+                      float acc_init, bool strict, const DeviceCtx *ctx, cudaStream_t st);
+
 namespace {
 
 constexpr int THREADS = 256;
@@ -42,50 +51,6 @@ struct ResizeArgs {
     int src_pitch;              // bytes per staged source row
     int tmp_pitch;              // floats per intermediate row
 };
-
-// ---- packed f32x2 arithmetic (sm_100+: FFMA2 / FADD2).  Same FLOP rate as the scalar forms
-// but half the issue slots, which is what these issue-bound passes are short of. ----
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pack2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
-__device__ __forceinline__ void unpack2(f32x2 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
-
-// 32-bit word of subpixels -> floats.  Integer subpixels are converted with the 2^23 trick
-// (PRMT builds the float 8388608 + v, one FADD removes the bias: exact) because I2F issues on
-// the quarter-rate XU pipe (measured 15 lanes/clk/SM vs > 34 for PRMT + FADD), which made the
-// vertical pass XU-bound in the first profile.
-template <typename T> struct Word;
-template <> struct Word<uint8_t> {
-    static constexpr int N = 4;
-    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[4]) {  // 2^23 + v
-        f[0] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7540));
-        f[1] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7541));
-        f[2] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7542));
-        f[3] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7543));
-    }
-};
-template <> struct Word<uint16_t> {
-    static constexpr int N = 2;
-    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[2]) {
-        f[0] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7510));
-        f[1] = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7532));
-    }
-};
-template <> struct Word<float> {
-    static constexpr int N = 1;
-    static __device__ __forceinline__ void biased(uint32_t w, float (&f)[1]) { f[0] = __uint_as_float(w); }
-};
-template <typename T> __device__ __forceinline__ float unbias(float m) { return m - 8388608.0f; }
-template <> __device__ __forceinline__ float unbias<float>(float m) { return m; }
-
-__device__ __forceinline__ void cp_async(void *smem_dst, const void *gsrc, int bytes) {
-    const uint32_t d = smem_u32(smem_dst);
-    if (bytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
-    else if (bytes == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(d), "l"(gsrc) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // One CTA = one TW x TH tile of the destination of one image (grid: x = tile column, y = tile
 // row, z = image).
@@ -544,6 +509,13 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     a.hleft = ht->d_left; a.hcount = ht->d_count; a.hw = ht->d_w; a.hstride = ht->host.stride;
     a.acc_init = acc_init;
     const bool strict = (flags & B200IMG_FP_STRICT) != 0;
+
+    if (!(flags & (B200IMG_RESIZE_UNFUSED | B200IMG_RESIZE_TILED))) {
+        rc = resize_stream_try(src, a.src_img_stride, src_row0, w, C, dtype, dst, a.dst_img_stride, dst_row0, dst_rows, nw,
+                               n_images, vt->host, vt->d_left, vt->d_count, vt->d_w, ht->host, ht->d_left, ht->d_count,
+                               ht->d_w, acc_init, strict, ctx, st);
+        if (rc != 0) return rc < 0 ? rc : B200IMG_OK;
+    }
 
     Plan p;
     const size_t budget = std::min<size_t>(ctx->smem_optin, 160 * 1024);

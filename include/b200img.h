@@ -75,6 +75,9 @@ typedef enum {
  * tile kernel.  Chosen automatically when a downscale is so extreme that a
  * tile's source footprint does not fit shared memory. */
 #define B200IMG_RESIZE_UNFUSED 256
+/* Resampler only: use the tile kernel even where the column-streaming kernel (downscales of
+ * u8 / u16 images) applies.  Same results; exists so that both kernels can be tested. */
+#define B200IMG_RESIZE_TILED 512
 
 const char *b200img_last_error(void);
 int b200img_version(void);

@@ -12,10 +12,10 @@ pytestmark = pytest.mark.gpu
 FILTERS = list(FilterType)
 
 
-def _check(img, nw, nh, f, cuda, acc_init=1.0, host=False, unfused=False):
+def _check(img, nw, nh, f, cuda, acc_init=1.0, host=False, unfused=False, tiled=False):
     import torch
     want = o.resize(img, nw, nh, int(f), acc_init=acc_init)
-    extra = L.RESIZE_UNFUSED if unfused else 0
+    extra = (L.RESIZE_UNFUSED if unfused else 0) | (L.RESIZE_TILED if tiled else 0)
     src = img if host else torch.from_numpy(img).to(cuda)
     strict = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_STRICT | extra)
     fast = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_FAST | extra)
@@ -104,6 +104,28 @@ def test_band_entry_point(cuda):
     L.check(lib.b200img_resize_band_src_rows(120, nh, 4, 100, 140, C.byref(s0), C.byref(sn)))
     assert lib.b200img_resize_band_dev(dev.data_ptr(), s0.value + 1, sn.value - 1, 70, 120, 4, L.F32, out.data_ptr(),
                                        100, 140, nw, nh, 4, 0.0, 0, None) == L.ERR_BAD_ARG
+
+
+@pytest.mark.parametrize("f", FILTERS)
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16])
+def test_tile_kernel_on_downscales(cuda, f, dtype):
+    """Downscales of integer images default to the streaming kernel; the tile kernel must agree."""
+    rng = np.random.default_rng(21)
+    for c in (1, 3, 4):
+        img = rand_image(rng, 90, 140, c, dtype)
+        _check(img, 61, 37, f, cuda, tiled=True)
+        _check(img, 33, 20, f, cuda, tiled=True, acc_init=0.0)
+
+
+def test_streaming_kernel_shapes(cuda):
+    """Strips, bands and ragged edges of the streaming kernel: many bands, several strips, odd sizes."""
+    rng = np.random.default_rng(22)
+    for (h, w, c, nh, nw, f) in [(700, 900, 4, 233, 301, FilterType.Lanczos3), (513, 1027, 3, 100, 257, FilterType.CatmullRom),
+                                 (1024, 1024, 4, 256, 256, FilterType.CatmullRom), (300, 2000, 1, 299, 500, FilterType.Triangle),
+                                 (257, 64, 2, 17, 63, FilterType.Gaussian), (1080, 1920, 4, 540, 960, FilterType.Lanczos3)]:
+        _check(rand_image(rng, h, w, c, np.uint8), nw, nh, f, cuda)
+    _check(rand_image(rng, 400, 333, 4, np.uint16), 111, 160, FilterType.Lanczos3, cuda)
+    _check(rand_image(rng, 400, 334, 3, np.uint16), 112, 90, FilterType.Triangle, cuda, acc_init=0.0)
 
 
 @pytest.mark.parametrize("f", FILTERS)
