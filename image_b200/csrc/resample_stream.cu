@@ -7,10 +7,13 @@
 // from global memory -- no staging), converted once, and multiplied into the accumulators of all
 // output rows whose vertical window is open (vertical_sample, src/imageops/sample.rs:494-562:
 // accumulator starts at acc_init, taps ascending -- the streaming order IS the reference order).
-// Output rows occupy A accumulator slots round-robin (row o -> slot o mod A); the per-source-row
-// weights of the A slots (zero where a slot's window is closed) are laid out densely in shared
-// memory so the inner loop has no branches.  When a window closes its accumulators are flushed
-// to an 8-row ring of the f32 intermediate in shared memory; every 8 finished rows the CTA runs
+// Source rows are taken in chunks of 4.  Within a chunk the destination rows whose windows are
+// still open occupy accumulator slots 0, 1, .. in order (slot s = row base(chunk) + s, base = rows
+// already finished); the per-source-row weights of the A slots (zero where a slot has no open
+// window) are laid out densely in shared memory so the inner loop has no branches.  After a chunk
+// the rows whose windows closed are flushed from slot 0 and the accumulators shift down, so
+// slot numbers never need run-time register indexing.  Flushed rows go to an 8-row ring of the
+// f32 intermediate in shared memory; every 8 finished rows the CTA runs
 // the horizontal pass (horizontal_sample, sample.rs:217-340) on them and stores 8 destination rows.
 // The intermediate never leaves the SM; DRAM sees the source once and the destination once.
 #include "common.cuh"
@@ -48,12 +51,13 @@ resize_stream_kernel(const StreamArgs a) {
     constexpr int N = Word<T>::N;
     constexpr bool PACKED = !STRICT;  // FFMA2 path
     extern __shared__ __align__(16) unsigned char smem[];
-    float2 *s_ws = reinterpret_cast<float2 *>(smem);                           // [max_band_rows][A] (w, w)
-    float *s_tmp = reinterpret_cast<float *>(s_ws + (size_t)a.max_band_rows * A);  // [ST_TH][tmp_pitch]
+    float2 *s_ws = reinterpret_cast<float2 *>(smem);                           // [max_band_rows + ST_PF][A] (w, w)
+    float *s_tmp = reinterpret_cast<float *>(s_ws + (size_t)(a.max_band_rows + ST_PF) * A);  // [ST_TH][tmp_pitch]
     float2 *s_hw = reinterpret_cast<float2 *>(s_tmp + (size_t)ST_TH * a.tmp_pitch);  // [hstride][TW] (w, w)
     int *s_hl = reinterpret_cast<int *>(s_hw + (size_t)a.TW * a.hstride);        // [TW]
     int *s_end = s_hl + a.TW;                                                    // [BAND] window end rows
-    T *s_out = reinterpret_cast<T *>(s_end + a.BAND);                            // [ST_TH][TW * C]
+    int *s_base = s_end + a.BAND;                                                // [chunks + 1] rows finished before a chunk
+    T *s_out = reinterpret_cast<T *>(s_base + (a.max_band_rows / ST_PF + 3));    // [ST_TH][TW * C]
 
     const int tid = threadIdx.x;
     const unsigned img = blockIdx.z;
@@ -82,18 +86,29 @@ resize_stream_kernel(const StreamArgs a) {
     }
     for (int i = tid; i < tw; i += ST_THREADS) s_hl[i] = a.hleft[ox0 + i] * C - sub0;
     for (int i = tid; i < nout; i += ST_THREADS) s_end[i] = a.vleft[oyA + i] + a.vcount[oyA + i];
-    for (int i = tid; i < (rowB - rowA) * A; i += ST_THREADS) s_ws[i] = make_float2(0.0f, 0.0f);
+    for (int i = tid; i < (rowB - rowA + ST_PF) * A; i += ST_THREADS) s_ws[i] = make_float2(0.0f, 0.0f);
+    const int chunks = (rowB - rowA + ST_PF - 1) / ST_PF;
+    for (int c = tid; c <= chunks; c += ST_THREADS) {  // base(c) = rows of the band whose window ends at or before the chunk starts
+        const int start = rowA + c * ST_PF;
+        int lo_ = 0, hi_ = nout;  // window ends are non-decreasing: binary search
+        while (lo_ < hi_) {
+            const int mid = (lo_ + hi_) >> 1;
+            if (a.vleft[oyA + mid] + a.vcount[oyA + mid] <= start) lo_ = mid + 1; else hi_ = mid;
+        }
+        s_base[c] = lo_;
+    }
     __syncthreads();
     for (int i = tid; i < nout * a.vstride; i += ST_THREADS) {
         const int o = i / a.vstride, k = i - o * a.vstride;
         if (k < a.vcount[oyA + o]) {
             const float w = a.vw[(size_t)(oyA + o) * a.vstride + k];
-            s_ws[(size_t)(a.vleft[oyA + o] + k - rowA) * A + (o % A)] = make_float2(w, w);
+            const int jr = a.vleft[oyA + o] + k - rowA;
+            s_ws[(size_t)jr * A + (o - s_base[jr / ST_PF])] = make_float2(w, w);
         }
     }
     __syncthreads();
 
-    // ---- accumulators: slot s holds destination row o with o mod A == s while its window is open ----
+    // ---- accumulators: within a chunk, slot s holds destination row base(chunk) + s ----
     f32x2 lo[A], hi[A];   // PACKED: (sub 0,1) and (sub 2,3)
     float acc[A][N];      // scalar path
     const f32x2 init2 = pack2(a.acc_init, a.acc_init);
@@ -158,42 +173,36 @@ resize_stream_kernel(const StreamArgs a) {
         }
     };
 
-    int next_out = 0, slot = 0;
-    int next_end = s_end[0];
+    int next_out = 0;
 
-    auto flush = [&]() {
-        // window of destination row oyA + next_out just closed: its accumulators go to the ring
+    auto flush_one = [&]() {
+        // the oldest open window (slot 0, destination row oyA + next_out) has closed
         float *t = s_tmp + (size_t)(next_out & (ST_TH - 1)) * a.tmp_pitch + tid * N;
-        switch (slot) {
-#define FLUSH_CASE(S)                                                                                          \
-    case S:                                                                                                    \
-        if constexpr (S < A) {                                                                                 \
-            if (active) {                                                                                      \
-                if constexpr (PACKED && N == 4) *reinterpret_cast<ulonglong2 *>(t) = make_ulonglong2(lo[S], hi[S]); \
-                else if constexpr (PACKED && N == 2) *reinterpret_cast<f32x2 *>(t) = lo[S];                    \
-                else {                                                                                         \
-                    _Pragma("unroll") for (int j = 0; j < N; ++j) t[j] = acc[S][j];                            \
-                }                                                                                              \
-            }                                                                                                  \
-            lo[S] = init2; hi[S] = init2;                                                                      \
-            _Pragma("unroll") for (int j = 0; j < N; ++j) acc[S][j] = a.acc_init;                              \
-        }                                                                                                      \
-        break;
-            FLUSH_CASE(0) FLUSH_CASE(1) FLUSH_CASE(2) FLUSH_CASE(3)
-            FLUSH_CASE(4) FLUSH_CASE(5) FLUSH_CASE(6) FLUSH_CASE(7)
-#undef FLUSH_CASE
+        if (active) {
+            if constexpr (PACKED && N == 4) *reinterpret_cast<ulonglong2 *>(t) = make_ulonglong2(lo[0], hi[0]);
+            else if constexpr (PACKED && N == 2) *reinterpret_cast<f32x2 *>(t) = lo[0];
+            else {
+#pragma unroll
+                for (int j = 0; j < N; ++j) t[j] = acc[0][j];
+            }
         }
-        slot = slot + 1 == A ? 0 : slot + 1;
+#pragma unroll
+        for (int s = 0; s + 1 < A; ++s) {
+            lo[s] = lo[s + 1]; hi[s] = hi[s + 1];
+#pragma unroll
+            for (int j = 0; j < N; ++j) acc[s][j] = acc[s + 1][j];
+        }
+        lo[A - 1] = init2; hi[A - 1] = init2;
+#pragma unroll
+        for (int j = 0; j < N; ++j) acc[A - 1][j] = a.acc_init;
         ++next_out;
-        next_end = next_out < nout ? s_end[next_out] : -1;
         if ((next_out & (ST_TH - 1)) == 0 || next_out == nout) {
             const int rows_g = (next_out & (ST_TH - 1)) ? (next_out & (ST_TH - 1)) : ST_TH;
             horizontal(next_out - rows_g, rows_g);
         }
     };
 
-    auto accumulate = [&](uint32_t wv, int j) {
-        const float2 *ws = s_ws + (size_t)(j - rowA) * A;
+    auto accumulate = [&](uint32_t wv, const float2 *ws) {
         if constexpr (PACKED && N == 4) {
             float f[4];
             Word<T>::biased(wv, f);
@@ -224,26 +233,28 @@ resize_stream_kernel(const StreamArgs a) {
         }
     };
 
-    // ---- stream down the band's source rows, ST_PF rows in flight per thread ----
+    // ---- stream down the band's source rows in chunks of ST_PF; the next chunk's loads are in
+    // flight while this one is accumulated.  Windows that closed inside a chunk are flushed after
+    // it (the rows in between carry zero weights for their slots). ----
+    const unsigned char *p = gcol;
     uint32_t cur[ST_PF], nxt[ST_PF];
 #pragma unroll
     for (int k = 0; k < ST_PF; ++k) {
         cur[k] = 0;
-        if (active && rowA + k < rowB) cur[k] = __ldg(reinterpret_cast<const uint32_t *>(gcol + (size_t)k * gp));
+        if (active && rowA + k < rowB) cur[k] = __ldg(reinterpret_cast<const uint32_t *>(p));
+        p += gp;
     }
     for (int j = rowA; j < rowB; j += ST_PF) {
 #pragma unroll
         for (int k = 0; k < ST_PF; ++k) {
             nxt[k] = 0;
-            if (active && j + ST_PF + k < rowB) nxt[k] = __ldg(reinterpret_cast<const uint32_t *>(gcol + (size_t)(j - rowA + ST_PF + k) * gp));
+            if (active && j + ST_PF + k < rowB) nxt[k] = __ldg(reinterpret_cast<const uint32_t *>(p));
+            p += gp;
         }
+        const float2 *ws = s_ws + (size_t)(j - rowA) * A;  // rows past rowB have zeroed weights (see set-up)
 #pragma unroll
-        for (int k = 0; k < ST_PF; ++k) {
-            if (j + k < rowB) {
-                accumulate(cur[k], j + k);
-                while (j + k + 1 == next_end) flush();
-            }
-        }
+        for (int k = 0; k < ST_PF; ++k) accumulate(cur[k], ws + k * A);
+        for (int f = s_base[(j - rowA) / ST_PF + 1] - next_out; f > 0; --f) flush_one();
 #pragma unroll
         for (int k = 0; k < ST_PF; ++k) cur[k] = nxt[k];
     }
@@ -251,15 +262,24 @@ resize_stream_kernel(const StreamArgs a) {
 
 int round_up_i(int v, int m) { return (v + m - 1) / m * m; }
 
-// smallest A in {4, 6, 8} such that rows o and o + A never have overlapping windows; 0 if none
-int slots_needed(const AxisTable &vt, uint32_t first, uint32_t count) {
-    static const int cand[] = {4, 6, 8};
-    for (int A : cand) {
-        bool ok = true;
-        for (uint32_t o = first; o + A < first + count && ok; ++o)
-            ok = vt.left[o + A] >= vt.left[o] + vt.count[o];
-        if (ok) return A;
+// Accumulator slots the kernel needs: the largest number of destination rows with a window
+// overlapping one 4-row chunk, over all bands.  Rounded up to a compiled size; 0 if > 12 (upscales).
+int slots_needed(const AxisTable &vt, uint32_t first, uint32_t count, int band) {
+    int need = 1;
+    for (uint32_t o0 = first; o0 < first + count; o0 += band) {
+        const uint32_t o1 = std::min<uint32_t>(o0 + band, first + count);
+        const int rowA = vt.left[o0], rowB = vt.left[o1 - 1] + vt.count[o1 - 1];
+        uint32_t base = o0, open_end = o0;  // [base, open_end): rows whose window overlaps the chunk
+        for (int start = rowA; start < rowB; start += ST_PF) {
+            while (base < o1 && vt.left[base] + vt.count[base] <= start) ++base;
+            while (open_end < o1 && vt.left[open_end] < start + ST_PF) ++open_end;
+            need = std::max(need, (int)(open_end - base));
+            if (need > 12) return 0;
+        }
     }
+    static const int cand[] = {4, 6, 8, 10, 12};
+    for (int A : cand)
+        if (need <= A) return A;
     return 0;
 }
 
@@ -287,7 +307,9 @@ int launch_c(const StreamArgs &a, int A, size_t smem, dim3 grid, bool strict, cu
     switch (A) {
         case 4: return launch_a<T, C, 4>(a, smem, grid, strict, st);
         case 6: return launch_a<T, C, 6>(a, smem, grid, strict, st);
-        default: return launch_a<T, C, 8>(a, smem, grid, strict, st);
+        case 8: return launch_a<T, C, 8>(a, smem, grid, strict, st);
+        case 10: return launch_a<T, C, 10>(a, smem, grid, strict, st);
+        default: return launch_a<T, C, 12>(a, smem, grid, strict, st);
     }
 }
 
@@ -314,9 +336,9 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
     const int tsize = (int)dtype_size(dtype);
     const size_t gp = (size_t)w * C * tsize;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
-    // downscales only: every source row is then tapped by at most 8 destination rows
-    const int A = slots_needed(vt, dst_row0, dst_rows);
-    if (A == 0 || vt.max_count < 2) return 0;
+    if (vt.max_count < 2) return 0;  // Nearest: nothing to share between rows; the tile kernel is fine
+    // a quick reject for upscales before the exact count below
+    if ((uint64_t)vt.left.size() > 0 && dst_rows > 12 && vt.left[dst_row0 + 12] - vt.left[dst_row0] < 1) return 0;
 
     int TW = 0;
     for (int cand = 128; cand >= 8; cand -= 8)
@@ -330,6 +352,8 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
     while (BAND > 16 && (uint64_t)strips * ((dst_rows + BAND - 1) / BAND) * n_images < (uint64_t)ctx->sm_count * 6) BAND /= 2;
     const int bands = (int)((dst_rows + BAND - 1) / BAND);
     if (bands > 65535 || n_images > 65535) return 0;
+    const int A = slots_needed(vt, dst_row0, dst_rows, BAND);
+    if (A == 0) return 0;
     int max_band_rows = 1;
     for (uint32_t o = dst_row0; o < dst_row0 + dst_rows; o += BAND) {
         const uint32_t e = std::min<uint32_t>(o + BAND, dst_row0 + dst_rows) - 1;
@@ -345,8 +369,8 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
     int tp = round_up_i(ST_THREADS * (4 / tsize), 4);
     if ((tp / 4) % 2 == 0) tp += 4;  // odd number of 16-byte units: the 8-row lane pattern of the horizontal pass
     a.tmp_pitch = tp;
-    const size_t smem = (size_t)max_band_rows * A * 8 + (size_t)ST_TH * tp * 4 + (size_t)TW * ht.stride * 8 + (size_t)TW * 4 +
-                        (size_t)BAND * 4 + (size_t)ST_TH * TW * C * tsize + 64;
+    const size_t smem = (size_t)(max_band_rows + ST_PF) * A * 8 + (size_t)ST_TH * tp * 4 + (size_t)TW * ht.stride * 8 + (size_t)TW * 4 +
+                        (size_t)BAND * 4 + (size_t)(max_band_rows / ST_PF + 3) * 4 + (size_t)ST_TH * TW * C * tsize + 64;
     if (smem > ctx->smem_optin) return 0;
     const dim3 grid((unsigned)strips, (unsigned)bands, n_images);
     int rc;
