@@ -62,7 +62,7 @@ template <> struct Box<float> {
 constexpr int V_BAND = 64;  // rows per thread
 
 template <typename T>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, 5)
 box_v_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, uint32_t n_images, int bands) {
     typedef typename Box<T>::sum_t S;
     constexpr int N = 4 / sizeof(T);  // subpixels per 32-bit word
@@ -101,7 +101,21 @@ box_v_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, uint32_t
         const int lo = y0 - r, hi = y0 + r;
         const int nlo = lo < 0 ? -lo : 0, nhi = hi > hmax ? hi - hmax : 0;
         S v[N];
-        for (int y = max(lo, 0); y <= min(hi, hmax); ++y) {
+        // loads batched 8 deep: a load-use-per-iteration loop would serialise on DRAM latency
+        constexpr int PB = 8;
+        int y = max(lo, 0);
+        const int yend = min(hi, hmax);
+        for (; y + PB - 1 <= yend; y += PB) {
+            S vb[PB][N];
+#pragma unroll
+            for (int k = 0; k < PB; ++k) load(y + k, vb[k]);
+#pragma unroll
+            for (int k = 0; k < PB; ++k) {
+#pragma unroll
+                for (int j = 0; j < N; ++j) sum[j] += vb[k][j];
+            }
+        }
+        for (; y <= yend; ++y) {
             load(y, v);
 #pragma unroll
             for (int j = 0; j < N; ++j) sum[j] += v[j];
@@ -171,8 +185,16 @@ __device__ __forceinline__ void copy_row_phased(const T *from, T *to, int n, int
     if (lane < head) to[lane] = from[lane];
     const uint32_t *vs = reinterpret_cast<const uint32_t *>(from + head);
     uint32_t *vd = reinterpret_cast<uint32_t *>(to + head);
+    if constexpr (TO_SHARED) {
+        // asynchronous 4-byte copies: every word of the row is in flight at once, no registers held
+        for (int v = lane; v < body; v += 32) {
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(vd + v);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(vs + v) : "memory");
+        }
+    } else {
 #pragma unroll 4
-    for (int v = lane; v < body; v += 32) vd[v] = vs[v];
+        for (int v = lane; v < body; v += 32) vd[v] = vs[v];
+    }
     const int done = head + body * PER;
     if (lane < n - done) to[done + lane] = from[done + lane];
 }
@@ -215,6 +237,7 @@ box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t t
             }
         }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
     const int chunks = (tw + H_XC - 1) / H_XC;
