@@ -210,7 +210,7 @@ def run_b200(args):
     }
 
     # ---- extras: the other hot-path families at their BASELINE shapes (rank 0 numbers, per GPU) ----
-    if not args.no_extras:
+    if not args.no_extras and world == 1:
         out["extra"] = extras(torch, lib, L, dev, stream, hbm, max(3, args.steps // 2), 3, FilterType, GaussianBlurParameters)
     # ---- CPU baseline (rank 0, N=1 only) ----
     if world == 1 and not args.no_cpu:

@@ -113,3 +113,12 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "import oracle" not in txt and "liboracle" not in txt and "oracle/" not in txt, f
+
+
+def test_rust_ffi_declares_every_header_symbol():
+    """rust/image-b200/src/ffi.rs (authored, not compilable here) stays in step with the header."""
+    hdr = open(os.path.join(ROOT, "include", "b200img.h")).read()
+    rs = open(os.path.join(ROOT, "rust", "image-b200", "src", "ffi.rs")).read()
+    declared = set(re.findall(r"\b(b200img_[a-z0-9_]+)\s*\(", hdr))
+    bound = set(re.findall(r"fn (b200img_[a-z0-9_]+)", rs))
+    assert declared == bound, declared ^ bound
