@@ -62,13 +62,16 @@ SIGNATURES = {
     "b200img_resize": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i, _f, _i]),
     "b200img_resize_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i, _f, _i, _vp]),
     "b200img_resize_batch_dev": (_i, [_vp, _sz, _u32, _u32, _i, _i, _vp, _sz, _u32, _u32, _u32, _i, _f, _i, _vp]),
+    "b200img_resize_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _u32, _i, _f, _i]),
     "b200img_resize_band_src_rows": (_i, [_u32, _u32, _i, _u32, _u32, _pu32, _pu32]),
     "b200img_resize_band_dev": (_i, [_vp, _u32, _u32, _u32, _u32, _i, _i, _vp, _u32, _u32, _u32, _u32, _i, _f, _i, _vp]),
     "b200img_gaussian_blur": (_i, [_vp, _u32, _u32, _i, _i, _vp, _P, _i, _i]),
     "b200img_gaussian_blur_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _P, _i, _i, _vp]),
+    "b200img_gaussian_blur_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _P, _i, _i]),
     "b200img_gaussian_blur_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _P, _i, _i, _vp]),
     "b200img_fast_blur": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f]),
     "b200img_fast_blur_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
+    "b200img_fast_blur_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f]),
     "b200img_fast_blur_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f, _vp]),
     "b200img_fast_blur_noalloc_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
     "b200img_convert": (_i, [_vp, _i, _i, _vp, _i, _i, _sz, _i, _vp]),

@@ -141,6 +141,78 @@ struct HostCall {
     }
 };
 
+// ---- host-resident batches: H2D, kernels and D2H of consecutive images overlap on three streams ----
+struct HostPipe {
+    static constexpr int SLOTS = 3;
+    cudaStream_t h2d = nullptr, exec = nullptr, d2h = nullptr;
+    cudaEvent_t e_in[SLOTS] = {}, e_run[SLOTS] = {}, e_out[SLOTS] = {};
+    void *src[SLOTS] = {}, *dst[SLOTS] = {};
+    size_t src_bytes = 0, dst_bytes = 0;
+    bool ready = false;
+};
+static std::map<int, HostPipe> g_pipes;  // guarded by g_host_api_mu
+
+static int pipe_get(size_t sb, size_t db, HostPipe **out) {
+    int dev;
+    B200_CUDA(cudaGetDevice(&dev));
+    HostPipe &p = g_pipes[dev];
+    if (!p.ready) {
+        B200_CUDA(cudaStreamCreateWithFlags(&p.h2d, cudaStreamNonBlocking));
+        B200_CUDA(cudaStreamCreateWithFlags(&p.exec, cudaStreamNonBlocking));
+        B200_CUDA(cudaStreamCreateWithFlags(&p.d2h, cudaStreamNonBlocking));
+        for (int i = 0; i < HostPipe::SLOTS; ++i) {
+            B200_CUDA(cudaEventCreateWithFlags(&p.e_in[i], cudaEventDisableTiming));
+            B200_CUDA(cudaEventCreateWithFlags(&p.e_run[i], cudaEventDisableTiming));
+            B200_CUDA(cudaEventCreateWithFlags(&p.e_out[i], cudaEventDisableTiming));
+        }
+        p.ready = true;
+    }
+    if (p.src_bytes < sb || p.dst_bytes < db) {
+        B200_CUDA(cudaDeviceSynchronize());
+        for (int i = 0; i < HostPipe::SLOTS; ++i) {
+            cudaFree(p.src[i]); cudaFree(p.dst[i]);
+            p.src[i] = p.dst[i] = nullptr;
+        }
+        p.src_bytes = p.dst_bytes = 0;
+        for (int i = 0; i < HostPipe::SLOTS; ++i) {
+            if (cudaMalloc(&p.src[i], sb) != cudaSuccess || cudaMalloc(&p.dst[i], db) != cudaSuccess) {
+                cudaGetLastError();
+                return fail(B200IMG_ERR_OOM, "cannot allocate the host-batch staging buffers (%zu + %zu bytes x %d)", sb, db, HostPipe::SLOTS);
+            }
+        }
+        p.src_bytes = sb; p.dst_bytes = db;
+    }
+    *out = &p;
+    return B200IMG_OK;
+}
+
+// op(d_src, d_dst, stream) enqueues the device work for one image.
+template <typename Op>
+static int pipe_run(const void *hsrc, size_t sb, void *hdst, size_t db, uint32_t n, Op op) {
+    std::lock_guard<std::mutex> lk(g_host_api_mu);
+    HostPipe *p;
+    int rc = pipe_get(sb, db, &p);
+    if (rc) return rc;
+    set_scratch_stream(p->exec);
+    for (uint32_t i = 0; i < n; ++i) {
+        const int s = (int)(i % HostPipe::SLOTS);
+        if (i >= (uint32_t)HostPipe::SLOTS) {
+            B200_CUDA(cudaStreamWaitEvent(p->h2d, p->e_run[s], 0));   // the slot's previous kernels have consumed src[s]
+            B200_CUDA(cudaStreamWaitEvent(p->exec, p->e_out[s], 0));  // and its previous result has left dst[s]
+        }
+        B200_CUDA(cudaMemcpyAsync(p->src[s], (const char *)hsrc + (size_t)i * sb, sb, cudaMemcpyHostToDevice, p->h2d));
+        B200_CUDA(cudaEventRecord(p->e_in[s], p->h2d));
+        B200_CUDA(cudaStreamWaitEvent(p->exec, p->e_in[s], 0));
+        if ((rc = op(p->src[s], p->dst[s], p->exec))) return rc;
+        B200_CUDA(cudaEventRecord(p->e_run[s], p->exec));
+        B200_CUDA(cudaStreamWaitEvent(p->d2h, p->e_run[s], 0));
+        B200_CUDA(cudaMemcpyAsync((char *)hdst + (size_t)i * db, p->dst[s], db, cudaMemcpyDeviceToHost, p->d2h));
+        B200_CUDA(cudaEventRecord(p->e_out[s], p->d2h));
+    }
+    B200_CUDA(cudaStreamSynchronize(p->d2h));
+    return B200IMG_OK;
+}
+
 static int check_image(const char *op, int channels, int dtype, uint32_t w, uint32_t h, size_t *bytes) {
     if (channels < 1 || channels > 4) return fail(B200IMG_ERR_BAD_ARG, "%s: channels must be 1..4 (got %d)", op, channels);
     if (!valid_dtype(dtype)) return fail(B200IMG_ERR_BAD_ARG, "%s: bad dtype %d", op, dtype);
@@ -364,6 +436,44 @@ int b200img_gaussian_blur(const void *src, uint32_t w, uint32_t h, int C, int dt
     if ((rc = hc.out_buf(bytes, &dd))) return rc;
     if ((rc = gaussian_blur_launch(ds, w, h, C, dtype, dd, 1, p, path, flags, 0))) return rc;
     return hc.out(dst, dd, bytes);
+}
+
+int b200img_gaussian_blur_batch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n,
+                                const b200img_gauss_params *p, int path, int flags) {
+    size_t bytes;
+    int rc = check_image("gaussian_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if ((rc = gauss_check(p, path))) return rc;
+    if (bytes == 0 || n == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: null buffer");
+    return pipe_run(src, bytes, dst, bytes, n, [&](void *ds, void *dd, cudaStream_t st) {
+        return gaussian_blur_launch(ds, w, h, C, dtype, dd, 1, p, path, flags, st);
+    });
+}
+
+int b200img_fast_blur_batch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n, float sigma) {
+    size_t bytes;
+    int rc = check_image("fast_blur", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0 || n == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "fast_blur: null buffer");
+    return pipe_run(src, bytes, dst, bytes, n, [&](void *ds, void *dd, cudaStream_t st) {
+        return fast_blur_launch(ds, w, h, C, dtype, dd, 1, sigma, st);
+    });
+}
+
+int b200img_resize_batch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                         uint32_t n, int filter, float acc_init, int flags) {
+    size_t sb, db;
+    int rc = check_image("resize", C, dtype, w, h, &sb);
+    if (rc) return rc;
+    if ((rc = check_image("resize", C, dtype, nw, nh, &db))) return rc;
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize: unknown filter %d", filter);
+    if (db == 0 || n == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "resize: null buffer");
+    return pipe_run(src, sb ? sb : 1, dst, db, n, [&](void *ds, void *dd, cudaStream_t st) {
+        return resize_front(ds, 0, w, h, C, dtype, dd, 0, nw, nh, 1, filter, acc_init, flags, st);
+    });
 }
 
 // ---- fast_blur ----------------------------------------------------------------

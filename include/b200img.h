@@ -141,6 +141,11 @@ int b200img_resize_batch_dev(const void *d_src, size_t src_stride, uint32_t w, u
                              int channels, int dtype, void *d_dst, size_t dst_stride,
                              uint32_t nw, uint32_t nh, uint32_t n_images, int filter,
                              float acc_init, int flags, void *stream);
+/* Host-resident batch: n_images equally-shaped, tightly packed images in HOST memory (pinned
+ * memory recommended).  Uploads, kernels and downloads of consecutive images overlap on three
+ * internal streams; returns when every result is in `dst`. */
+int b200img_resize_batch(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                         uint32_t nw, uint32_t nh, uint32_t n_images, int filter, float acc_init, int flags);
 /* One row band of a larger resize (multi-GPU single-image split): computes
  * destination rows [dst_row0, dst_row0 + dst_rows) of the nw x nh result.
  * d_src_band holds source rows [src_row0, src_row0 + src_rows) of the w x h
@@ -169,6 +174,9 @@ int b200img_gaussian_blur(const void *src, uint32_t w, uint32_t h, int channels,
 int b200img_gaussian_blur_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
                               void *d_dst, const b200img_gauss_params *params, int path,
                               int flags, void *stream);
+/* host-resident batch, pipelined like b200img_resize_batch */
+int b200img_gaussian_blur_batch(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                                uint32_t n_images, const b200img_gauss_params *params, int path, int flags);
 int b200img_gaussian_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int channels,
                                     int dtype, void *d_dst, uint32_t n_images,
                                     const b200img_gauss_params *params, int path, int flags,
@@ -182,6 +190,9 @@ int b200img_fast_blur(const void *src, uint32_t w, uint32_t h, int channels, int
                       void *dst, float sigma);
 int b200img_fast_blur_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
                           void *d_dst, float sigma, void *stream);
+/* host-resident batch, pipelined like b200img_resize_batch */
+int b200img_fast_blur_batch(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                            uint32_t n_images, float sigma);
 int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int channels,
                                 int dtype, void *d_dst, uint32_t n_images, float sigma,
                                 void *stream);

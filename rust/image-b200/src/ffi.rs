@@ -52,6 +52,8 @@ extern "C" {
     pub fn b200img_resize_batch_dev(src: *const c_void, src_stride: usize, w: u32, h: u32, channels: c_int, dtype: c_int,
                                     dst: *mut c_void, dst_stride: usize, nw: u32, nh: u32, n_images: u32, filter: c_int,
                                     acc_init: c_float, flags: c_int, stream: Stream) -> c_int;
+    pub fn b200img_resize_batch(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                nw: u32, nh: u32, n_images: u32, filter: c_int, acc_init: c_float, flags: c_int) -> c_int;
     pub fn b200img_resize_band_src_rows(h: u32, nh: u32, filter: c_int, dst_row0: u32, dst_rows: u32,
                                         src_row0: *mut u32, src_rows: *mut u32) -> c_int;
     pub fn b200img_resize_band_dev(src_band: *const c_void, src_row0: u32, src_rows: u32, w: u32, h: u32, channels: c_int,
@@ -62,6 +64,8 @@ extern "C" {
                                  params: *const b200img_gauss_params, path: c_int, flags: c_int) -> c_int;
     pub fn b200img_gaussian_blur_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                                      params: *const b200img_gauss_params, path: c_int, flags: c_int, stream: Stream) -> c_int;
+    pub fn b200img_gaussian_blur_batch(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                       n_images: u32, params: *const b200img_gauss_params, path: c_int, flags: c_int) -> c_int;
     pub fn b200img_gaussian_blur_batch_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,
                                            dst: *mut c_void, n_images: u32, params: *const b200img_gauss_params,
                                            path: c_int, flags: c_int, stream: Stream) -> c_int;
@@ -70,6 +74,8 @@ extern "C" {
                              sigma: c_float) -> c_int;
     pub fn b200img_fast_blur_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                                  sigma: c_float, stream: Stream) -> c_int;
+    pub fn b200img_fast_blur_batch(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                   n_images: u32, sigma: c_float) -> c_int;
     pub fn b200img_fast_blur_batch_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                                        n_images: u32, sigma: c_float, stream: Stream) -> c_int;
     pub fn b200img_fast_blur_noalloc_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,

@@ -129,3 +129,30 @@ def test_fast_blur_constant_image_property_4k(cuda):
     assert int(out.min()) == 143 and int(out.max()) == 143
     out = DynamicImage(ImageBuffer(img)).blur_advanced(GaussianBlurParameters.new_from_sigma(10.0)).buf.data
     assert int(out.min()) == 143 and int(out.max()) == 143
+
+
+def test_host_batch_entry_points_match_single_calls(cuda):
+    """b200img_*_batch (host-resident, pipelined on three streams) == the per-image host calls."""
+    import ctypes as C
+    lib = L.lib()
+    rng = np.random.default_rng(50)
+    n, h, w, c = 7, 61, 90, 3  # more images than pipeline slots
+    batch = rng.integers(0, 256, (n, h, w, c), dtype=np.uint8)
+    p = GaussianBlurParameters.new_from_sigma(2.2)
+    out = np.empty_like(batch)
+    L.check(lib.b200img_gaussian_blur_batch(batch.ctypes.data, w, h, c, L.U8, out.ctypes.data, n, C.byref(p.raw), L.BLUR_GENERIC, L.FP_FAST))
+    for i in range(n):
+        assert np.array_equal(out[i], imageops.blur_advanced(batch[i], p)), i
+    L.check(lib.b200img_fast_blur_batch(batch.ctypes.data, w, h, c, L.U8, out.ctypes.data, n, 3.0))
+    for i in range(n):
+        assert np.array_equal(out[i], o.fast_blur(batch[i], 3.0)), i
+    small = np.empty((n, 20, 33, c), np.uint8)
+    L.check(lib.b200img_resize_batch(batch.ctypes.data, w, h, c, L.U8, small.ctypes.data, 33, 20, n, 4, 1.0, L.FP_STRICT))
+    for i in range(n):
+        assert np.array_equal(small[i], o.resize(batch[i], 33, 20, "lanczos3")), i
+    # a second, larger call re-sizes the staging buffers
+    big = rng.integers(0, 256, (4, 200, 300, 4), dtype=np.uint8)
+    outb = np.empty_like(big)
+    L.check(lib.b200img_fast_blur_batch(big.ctypes.data, 300, 200, 4, L.U8, outb.ctypes.data, 4, 5.0))
+    for i in range(4):
+        assert np.array_equal(outb[i], o.fast_blur(big[i], 5.0)), i
