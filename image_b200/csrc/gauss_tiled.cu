@@ -20,6 +20,7 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cstring>
 #include <type_traits>
 
 namespace b200 {
@@ -262,10 +263,20 @@ col_tiled_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
 }
 
 // ---- f32 engine, FFMA2 kernels ------------------------------------------------------------------
+// They also run the Q0.15 engine for u8 pixels: weights <= 32767 and pixels <= 255 are integers,
+// every product is < 2^23 and every partial sum <= 255 * 32768 < 2^24, so f32 arithmetic on them
+// is exact in any order and the kernel is bit-identical to the reference's u32 accumulator
+// (src/imageops/filter_1d.rs:132-150, 396-408).  (Not so for u16: 65535 * 32767 needs 31 bits.)
+template <typename Out, bool Q15> struct StF;
+template <typename Out> struct StF<Out, false> { static __device__ __forceinline__ Out f(float a) { return St<Out, float>::f(a); } };
+template <> struct StF<uint8_t, true> {
+    static __device__ __forceinline__ uint8_t f(float a) { return (uint8_t)min((__float2uint_rz(a) + 16384u) >> 15, 255u); }
+};
+
 // Row pass: lane = row, warp item = (pixel blocks xb and xb + 4, channel): 16 outputs per thread.
-template <typename In, int C>
+template <typename In, typename Mid, int C, bool Q15>
 __global__ void __launch_bounds__(GT_THREADS)
-row_f32x2_kernel(const In *__restrict__ src, float *__restrict__ mid, uint32_t W, size_t total_rows, int half,
+row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, size_t total_rows, int half,
                  int shift, int nch, int in_pitch, const __grid_constant__ TapWeights2 tw) {
     constexpr int OUT_PITCH = (ROW_XT * C) | 1;
     extern __shared__ __align__(16) uint32_t sm[];
@@ -330,17 +341,17 @@ row_f32x2_kernel(const In *__restrict__ src, float *__restrict__ mid, uint32_t W
     for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
         const size_t row = row0 + r;
         if (row >= total_rows) break;
-        float *g = mid + row * g_pitch + (size_t)x0 * C;
+        Mid *g = mid + row * g_pitch + (size_t)x0 * C;
         const float *s = s_out + r * OUT_PITCH;
 #pragma unroll 4
-        for (int e = lane; e < out_elems; e += 32) g[e] = s[e];
+        for (int e = lane; e < out_elems; e += 32) g[e] = StF<Mid, Q15>::f(s[e]);
     }
 }
 
 // Column pass: thread = two adjacent subpixel columns x 8 rows; one LDS.64 per staged row.
-template <typename Out>
+template <typename Mid, typename Out, bool Q15>
 __global__ void __launch_bounds__(GT_THREADS)
-col_f32x2_kernel(const float *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
+col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
                  int nch, int zero_first_row, const __grid_constant__ TapWeights2 tw) {
     extern __shared__ __align__(16) uint32_t sm[];
     float *s = reinterpret_cast<float *>(sm);  // [COL_TH + nch*8 - 1][COL_TW]
@@ -349,10 +360,10 @@ col_f32x2_kernel(const float *__restrict__ mid, Out *__restrict__ dst, uint32_t 
     const uint32_t img = blockIdx.y / tiles_y;
     const int y0 = (int)(blockIdx.y % tiles_y) * COL_TH;
     const int sr = COL_TH + nch * GT_R - 1;
-    const float *m = mid + (size_t)img * H * row_sub;
+    const Mid *m = mid + (size_t)img * H * row_sub;
 
     // stage [sr][COL_TW] with clamped rows; 16-byte async copies when the rows allow it
-    const bool vec = (row_sub % 4 == 0) && (s0 + COL_TW <= row_sub) && ((reinterpret_cast<uintptr_t>(m) & 15) == 0);
+    const bool vec = sizeof(Mid) == 4 && (row_sub % 4 == 0) && (s0 + COL_TW <= row_sub) && ((reinterpret_cast<uintptr_t>(m) & 15) == 0);
     if (vec) {
         constexpr int VPR = COL_TW / 4;  // 16-byte vectors per staged row
         for (int i = tid; i < sr * VPR; i += GT_THREADS) {
@@ -367,7 +378,7 @@ col_f32x2_kernel(const float *__restrict__ mid, Out *__restrict__ dst, uint32_t 
         const uint32_t col = min(s0 + c, row_sub - 1);
         for (int r = tid / COL_TW; r < sr; r += GT_THREADS / COL_TW) {
             const int y = min(max(y0 - half + r, 0), (int)H - 1);
-            s[r * COL_TW + c] = m[(size_t)y * row_sub + col];
+            s[r * COL_TW + c] = (float)m[(size_t)y * row_sub + col];
         }
     }
     __syncthreads();
@@ -389,8 +400,8 @@ col_f32x2_kernel(const float *__restrict__ mid, Out *__restrict__ dst, uint32_t 
             unpack2(acc[r], v0, v1);
             Out *o = d + (size_t)y * row_sub + col;
             const bool z = zero_first_row && y == 0;
-            if (col < row_sub) o[0] = z ? (Out)0 : St<Out, float>::f(v0);
-            if (col + 1 < row_sub) o[1] = z ? (Out)0 : St<Out, float>::f(v1);
+            if (col < row_sub) o[0] = z ? (Out)0 : StF<Out, Q15>::f(v0);
+            if (col + 1 < row_sub) o[1] = z ? (Out)0 : StF<Out, Q15>::f(v1);
         }
     }
 }
@@ -402,6 +413,8 @@ template <typename T, typename Mid, typename Acc>
 int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
                     const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
                     cudaStream_t st) {
+    // Q0.15 on u8: exact in f32 (see StF), so it rides the FFMA2 kernels with integer-valued weights
+    constexpr bool Q15F = std::is_same<Acc, uint32_t>::value && std::is_same<T, uint8_t>::value;
     const int rnch = (rlen + GT_R - 1) / GT_R, cnch = (clen + GT_R - 1) / GT_R;
     const size_t total_rows = (size_t)h * n_images;
     const uint32_t row_sub = w * (uint32_t)C;
@@ -414,18 +427,23 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
     const dim3 row_grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
     const dim3 col_grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
 
-    if constexpr (std::is_same<Acc, float>::value) {
+    if constexpr (std::is_same<Acc, float>::value || Q15F) {
         TapWeights2 rwl, cwl;
         for (int i = 0; i < GT_MAX_TAPS; ++i) {
-            const uint32_t a = i < rlen ? rk[i] : 0u, b = i < clen ? ck[i] : 0u;
+            uint32_t a = i < rlen ? rk[i] : 0u, b = i < clen ? ck[i] : 0u;
+            if (Q15F) {  // integer weights -> the same integers as floats
+                const float fa = (float)a, fb = (float)b;
+                memcpy(&a, &fa, 4);
+                memcpy(&b, &fb, 4);
+            }
             rwl.w[i] = ((f32x2)a << 32) | a;
             cwl.w[i] = ((f32x2)b << 32) | b;
         }
 #define ROW_GO(CC)                                                                                                   \
     {                                                                                                                \
-        auto k = row_f32x2_kernel<T, CC>;                                                                            \
+        auto k = row_f32x2_kernel<T, Mid, CC, Q15F>;                                                                 \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem));              \
-        k<<<row_grid, GT_THREADS, row_smem, st>>>(src, (float *)mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rwl); \
+        k<<<row_grid, GT_THREADS, row_smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rwl); \
     }
         switch (C) {
             case 1: ROW_GO(1) break;
@@ -434,9 +452,9 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
             default: ROW_GO(4) break;
         }
 #undef ROW_GO
-        auto k = col_f32x2_kernel<T>;
+        auto k = col_f32x2_kernel<Mid, T, Q15F>;
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));
-        k<<<col_grid, GT_THREADS, col_smem, st>>>((const float *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl);
+        k<<<col_grid, GT_THREADS, col_smem, st>>>((const Mid *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl);
     } else {
         TapWeights rw, cw;
         for (int i = 0; i < GT_MAX_TAPS; ++i) { rw.w[i] = i < rlen ? rk[i] : 0u; cw.w[i] = i < clen ? ck[i] : 0u; }
