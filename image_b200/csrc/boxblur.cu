@@ -25,8 +25,14 @@
 #include "host_tables.h"
 
 #include <mutex>
+#include <type_traits>
 
 namespace b200 {
+
+// boxblur_u8.cu: word-at-a-time passes for u8 images (the common case)
+int box_pass_u8(const uint8_t *src, uint8_t *tmp, uint8_t *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t radius,
+                const DeviceCtx *ctx, cudaStream_t st);
+
 namespace {
 
 constexpr int THREADS = 256;
@@ -309,6 +315,11 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
         g.recip = UINT32_MAX / g.ks + 1u;
         g.bias = g.ks / 2;
         g.inv = 1.0f / (float)g.ks;
+        if constexpr (std::is_same<T, uint8_t>::value) {
+            const int rc = box_pass_u8((const uint8_t *)cur, (uint8_t *)tmp, (uint8_t *)dst, w, h, C, n_images, g.r, ctx, st);
+            if (rc < 0) return rc;
+            if (rc == 1) { cur = (const T *)dst; continue; }
+        }
         {
             // one staged element past the last window keeps the sliding update branch-free
             const int in_pitch = staged_pitch((H_XT + 2 * (int)g.r + 1) * C, sizeof(T));

@@ -1,0 +1,247 @@
+// boxblur_u8.cu -- the u8 box-blur passes of fast_blur, word-at-a-time.
+//
+// Same arithmetic as the reference's u8 accumulator (src/imageops/fast_blur.rs:36-71: u32 window
+// sums, store = ((sum + ks/2) * ceil(2^32/ks)) >> 32; horizontal pass 303-413, vertical pass
+// 416-473) -- window sums of integers, so bit-identical however they are accumulated -- but laid
+// out for the machine: the generic kernels in boxblur.cu spend ~20 instructions per subpixel on
+// byte-granular loads, stores and index arithmetic; here every shared/global access is a 32-bit
+// word and the per-byte work is two PRMTs, one IADD3 and one IMAD.HI.
+//
+//   vertical:   thread = one word column (4 subpixels) x a band of rows.  The four running sums
+//               live in two registers as 16-bit lanes (sum + ks/2 <= 255*255 + 127 < 2^16), so the
+//               sliding update is 4 PRMT + 2 IADD3 per row.
+//   horizontal: a CTA stages 32 rows x 256 pixels (+ halo) word-aligned in shared memory (funnel
+//               shift from the rows' global alignment); lane = row; a thread slides all C channel
+//               sums along a 64-pixel chunk in steps of 4 pixels = C whole words in, C whole words
+//               out, fully unrolled.
+// Taken when ks <= 255 and rows are 4-byte aligned; boxblur.cu's generic kernels cover the rest.
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+constexpr int V_THREADS = 256;
+constexpr int V_BAND = 64;
+constexpr int H_THREADS = 128;
+constexpr int H_ROWS = 32;
+constexpr int H_XT = 256;
+constexpr int H_XC = 64;
+
+struct U8Geom {
+    uint32_t w, h;
+    uint32_t r, ks, recip, bias;
+};
+
+__device__ __forceinline__ uint32_t even_lanes(uint32_t w) { return __byte_perm(w, 0, 0x4240); }  // [b0, 0, b2, 0]
+__device__ __forceinline__ uint32_t odd_lanes(uint32_t w) { return __byte_perm(w, 0, 0x4341); }   // [b1, 0, b3, 0]
+__device__ __forceinline__ uint32_t byte_of(uint32_t w, int j) { return __byte_perm(w, 0, 0x4440 + j); }
+
+// ---- vertical ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(V_THREADS)
+box_v_u8_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, U8Geom g, uint32_t words, int bands) {
+    const uint32_t wd = blockIdx.x * V_THREADS + threadIdx.x;
+    if (wd >= words) return;
+    const uint32_t img = blockIdx.y / bands, band = blockIdx.y % bands;
+    const int y0 = (int)band * V_BAND, y1 = min(y0 + V_BAND, (int)g.h);
+    const int r = (int)g.r, hmax = (int)g.h - 1;
+    const uint32_t *p = src + (size_t)img * g.h * words + wd;
+    uint32_t *d = dst + (size_t)img * g.h * words + wd;
+
+    // lanes carry sum + ks/2
+    uint32_t se = g.bias | (g.bias << 16), so = se;
+    {
+        const int lo = y0 - r, hi = y0 + r;
+        const int nlo = lo < 0 ? -lo : 0, nhi = hi > hmax ? hi - hmax : 0;
+        int y = max(lo, 0);
+        const int yend = min(hi, hmax);
+        constexpr int PB = 8;  // loads batched: a load-use-per-iteration loop serialises on DRAM latency
+        for (; y + PB - 1 <= yend; y += PB) {
+            uint32_t v[PB];
+#pragma unroll
+            for (int k = 0; k < PB; ++k) v[k] = __ldg(p + (size_t)(y + k) * words);
+#pragma unroll
+            for (int k = 0; k < PB; ++k) { se += even_lanes(v[k]); so += odd_lanes(v[k]); }
+        }
+        for (; y <= yend; ++y) { const uint32_t v = __ldg(p + (size_t)y * words); se += even_lanes(v); so += odd_lanes(v); }
+        if (nlo) { const uint32_t v = __ldg(p); se += even_lanes(v) * (uint32_t)nlo; so += odd_lanes(v) * (uint32_t)nlo; }
+        if (nhi) { const uint32_t v = __ldg(p + (size_t)hmax * words); se += even_lanes(v) * (uint32_t)nhi; so += odd_lanes(v) * (uint32_t)nhi; }
+    }
+    auto emit = [&](int y) {
+        const uint32_t b0 = __umulhi(se & 0xffffu, g.recip), b2 = __umulhi(se >> 16, g.recip);
+        const uint32_t b1 = __umulhi(so & 0xffffu, g.recip), b3 = __umulhi(so >> 16, g.recip);
+        d[(size_t)y * words] = __byte_perm(__byte_perm(b0, b1, 0x0040), __byte_perm(b2, b3, 0x0040), 0x5410);
+    };
+    constexpr int U = 4;
+    int y = y0;
+    for (; y + U <= y1; y += U) {
+        uint32_t a[U], b[U];
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            a[k] = __ldg(p + (size_t)min(y + k + r + 1, hmax) * words);
+            b[k] = __ldg(p + (size_t)max(y + k - r, 0) * words);
+        }
+#pragma unroll
+        for (int k = 0; k < U; ++k) {
+            emit(y + k);
+            se = se + even_lanes(a[k]) - even_lanes(b[k]);
+            so = so + odd_lanes(a[k]) - odd_lanes(b[k]);
+        }
+    }
+    for (; y < y1; ++y) {
+        emit(y);
+        const uint32_t a = __ldg(p + (size_t)min(y + r + 1, hmax) * words), b = __ldg(p + (size_t)max(y - r, 0) * words);
+        se = se + even_lanes(a) - even_lanes(b);
+        so = so + odd_lanes(a) - odd_lanes(b);
+    }
+}
+
+// ---- horizontal ----------------------------------------------------------------------------------
+template <int C>
+__global__ void __launch_bounds__(H_THREADS)
+box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Geom g, size_t total_rows, int in_pitch,
+                int out_pitch) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    uint32_t *s_in = sm;                                 // [H_ROWS][in_pitch] words; staged pixel 0 = source pixel x0 - r
+    uint32_t *s_out = sm + (size_t)H_ROWS * in_pitch;    // [H_ROWS][out_pitch] words; pixel 0 = x0
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int x0 = blockIdx.x * H_XT;
+    const size_t row0 = (size_t)blockIdx.y * H_ROWS;
+    const int r = (int)g.r, W = (int)g.w;
+    const int tw = min(H_XT, W - x0);
+    const int sp = tw + 2 * r;                           // staged pixels (clamped at the image edges)
+    const int sbytes = sp * C;
+    const int swords = (sbytes + 3) / 4;
+    const size_t g_pitch = (size_t)W * C;                // bytes; multiple of 4 (checked by the host)
+    const bool interior = x0 - r >= 0 && x0 + tw + r <= W;
+
+    for (int rr = warp; rr < H_ROWS; rr += H_THREADS / 32) {
+        const uint8_t *grow = src + min(row0 + rr, total_rows - 1) * g_pitch;
+        uint32_t *s = s_in + (size_t)rr * in_pitch;
+        if (interior) {
+            // word-aligned in shared memory whatever the global phase: funnel two aligned global words
+            const uint8_t *gb = grow + (size_t)(x0 - r) * C;
+            const int phase = (int)(reinterpret_cast<uintptr_t>(gb) & 3);
+            const uint32_t *gw = reinterpret_cast<const uint32_t *>(gb - phase);
+            for (int wi = lane; wi < swords; wi += 32) {
+                const uint32_t lo = __ldg(gw + wi);
+                const uint32_t hi = (phase && 4 * (wi + 1) < phase + sbytes) ? __ldg(gw + wi + 1) : 0u;
+                s[wi] = __funnelshift_r(lo, hi, phase * 8);
+            }
+        } else {
+            uint8_t *sb = reinterpret_cast<uint8_t *>(s);
+            for (int e = lane; e < sbytes; e += 32) {
+                const int p = e / C, c = e - p * C;
+                sb[e] = grow[(size_t)min(max(x0 - r + p, 0), W - 1) * C + c];
+            }
+        }
+    }
+    __syncthreads();
+
+    // lane = row; item = 64-pixel chunk; steps of 4 pixels = C words
+    const int chunks = (tw + H_XC - 1) / H_XC;
+    const uint32_t *in_row = s_in + (size_t)lane * in_pitch;
+    uint32_t *out_row = s_out + (size_t)lane * out_pitch;
+    const int nshift = ((2 * r + 1) * C) & 3;  // byte misalignment of the incoming pixels relative to the outgoing ones
+    for (int ck = warp; ck < chunks; ck += H_THREADS / 32) {
+        const int xa = ck * H_XC, xb = min(xa + H_XC, tw);
+        uint32_t sum[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) sum[c] = g.bias;
+        {
+            const uint8_t *b = reinterpret_cast<const uint8_t *>(in_row) + xa * C;
+            for (int j = 0; j <= 2 * r; ++j) {
+#pragma unroll
+                for (int c = 0; c < C; ++c) sum[c] += b[j * C + c];
+            }
+        }
+        const uint32_t *pw = in_row + (xa * C) / 4;                        // outgoing pixels: word aligned (xa % 4 == 0)
+        const uint32_t *nw = in_row + ((xa + 2 * r + 1) * C) / 4;          // incoming pixels: aligned down; shifted by nshift bytes
+        for (int x = xa; x < xb; x += 4) {
+            uint32_t prev[C], next[C], nraw[C + 1], outw[C];
+#pragma unroll
+            for (int k = 0; k < C; ++k) prev[k] = pw[k];
+#pragma unroll
+            for (int k = 0; k <= C; ++k) nraw[k] = nw[k];
+#pragma unroll
+            for (int k = 0; k < C; ++k) next[k] = __funnelshift_r(nraw[k], nraw[k + 1], nshift * 8);
+            uint32_t ob[4 * C];
+#pragma unroll
+            for (int b = 0; b < 4 * C; ++b) {
+                const int c = b % C;
+                ob[b] = __umulhi(sum[c], g.recip);
+                sum[c] = sum[c] + byte_of(next[b / 4], b & 3) - byte_of(prev[b / 4], b & 3);
+            }
+#pragma unroll
+            for (int k = 0; k < C; ++k)
+                outw[k] = __byte_perm(__byte_perm(ob[4 * k], ob[4 * k + 1], 0x0040), __byte_perm(ob[4 * k + 2], ob[4 * k + 3], 0x0040), 0x5410);
+            uint32_t *ow = out_row + (x * C) / 4;
+#pragma unroll
+            for (int k = 0; k < C; ++k) ow[k] = outw[k];
+            pw += C;
+            nw += C;
+        }
+    }
+    __syncthreads();
+
+    const int obytes = tw * C;
+    for (int rr = warp; rr < H_ROWS; rr += H_THREADS / 32) {
+        const size_t row = row0 + rr;
+        if (row >= total_rows) break;
+        uint8_t *gout = dst + row * g_pitch + (size_t)x0 * C;  // 4-byte aligned: g_pitch % 4 == 0, x0 % 4 == 0
+        const uint32_t *s = s_out + (size_t)rr * out_pitch;
+        const int full = obytes / 4;
+        for (int wi = lane; wi < full; wi += 32) reinterpret_cast<uint32_t *>(gout)[wi] = s[wi];
+        if (lane < obytes - 4 * full) gout[4 * full + lane] = reinterpret_cast<const uint8_t *>(s)[4 * full + lane];
+    }
+}
+
+int odd_words(int bytes) { return (((bytes + 3) / 4) | 1); }
+
+}  // namespace
+
+// One box pass (horizontal into tmp, vertical into dst) on u8 images.  Returns 1 if done, 0 if the
+// fast path does not apply (caller uses the generic kernels), < 0 on error.
+int box_pass_u8(const uint8_t *src, uint8_t *tmp, uint8_t *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t radius,
+                const DeviceCtx *ctx, cudaStream_t st) {
+    const uint32_t ks = 2 * radius + 1;
+    const size_t row_bytes = (size_t)w * C;
+    if (ks > 255 || row_bytes % 4 != 0) return 0;
+    if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(tmp) | reinterpret_cast<uintptr_t>(dst)) & 3) != 0) return 0;
+    U8Geom g;
+    g.w = w; g.h = h; g.r = radius; g.ks = ks;
+    g.recip = UINT32_MAX / ks + 1u;
+    g.bias = ks / 2;
+    const size_t total_rows = (size_t)h * n_images;
+    {
+        // slack: the last 4-pixel step reads up to C + 1 words past the last needed incoming pixel
+        const int in_pitch = odd_words((H_XT + 2 * (int)radius + 1 + 8) * C + 8);
+        const int out_pitch = odd_words((H_XT + 4) * C);
+        const size_t smem = (size_t)H_ROWS * (in_pitch + out_pitch) * 4;
+        if (smem > ctx->smem_optin) return 0;
+        const dim3 grid((w + H_XT - 1) / H_XT, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
+#define H_GO(CC)                                                                                        \
+    {                                                                                                   \
+        auto k = box_h_u8_kernel<CC>;                                                                   \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+        k<<<grid, H_THREADS, smem, st>>>(src, tmp, g, total_rows, in_pitch, out_pitch);                 \
+    }
+        switch (C) {
+            case 1: H_GO(1) break;
+            case 2: H_GO(2) break;
+            case 3: H_GO(3) break;
+            default: H_GO(4) break;
+        }
+#undef H_GO
+    }
+    {
+        const uint32_t words = (uint32_t)(row_bytes / 4);
+        const int bands = (int)((h + V_BAND - 1) / V_BAND);
+        const dim3 grid((words + V_THREADS - 1) / V_THREADS, (unsigned)(bands * n_images));
+        box_v_u8_kernel<<<grid, V_THREADS, 0, st>>>(reinterpret_cast<const uint32_t *>(tmp), reinterpret_cast<uint32_t *>(dst), g,
+                                                     words, bands);
+    }
+    B200_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace b200

@@ -94,11 +94,12 @@ __device__ __forceinline__ f32x2 pack2(float a, float b) { f32x2 r; asm("mov.b64
 __device__ __forceinline__ void unpack2(f32x2 v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
 __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
 
-// acc[r] = (sum_k A[(r+k)*STRIDE] w[k], sum_k B[(r+k)*STRIDE] w[k]).  PAIRED: B = A + 1 and A is
-// 8-byte aligned, so one LDS.64 fetches both.
-template <int STRIDE, bool PAIRED>
+// acc[r] = (sum_k A[(r+k)*STRIDE] w[k], sum_k B[(r+k)*STRIDE] w[k]), k < nch * TC.  PAIRED: B = A + 1
+// and A is 8-byte aligned, so one LDS.64 fetches both.  TC (taps per unrolled chunk) is chosen per
+// launch from {5,6,7,8} to minimise zero-padded taps (65 taps = 13 x 5, 21 = 3 x 7).
+template <int STRIDE, bool PAIRED, int TC>
 __device__ __forceinline__ void conv8x2(const float *inA, const float *inB, int nch, const TapWeights2 &tw, f32x2 (&acc)[GT_R]) {
-    f32x2 win[2 * GT_R - 1];
+    f32x2 win[GT_R - 1 + TC];
     auto ld = [&](int i) -> f32x2 {
         if constexpr (PAIRED) return *reinterpret_cast<const f32x2 *>(inA + i * STRIDE);
         else return pack2(inA[i * STRIDE], inB[i * STRIDE]);
@@ -110,17 +111,17 @@ __device__ __forceinline__ void conv8x2(const float *inA, const float *inB, int 
 #pragma unroll 1
     for (int ch = 0; ch < nch; ++ch) {
 #pragma unroll
-        for (int i = 0; i < GT_R; ++i) win[GT_R - 1 + i] = ld(i);
-        inA += GT_R * STRIDE;
-        inB += GT_R * STRIDE;
+        for (int i = 0; i < TC; ++i) win[GT_R - 1 + i] = ld(i);
+        inA += TC * STRIDE;
+        inB += TC * STRIDE;
 #pragma unroll
-        for (int kk = 0; kk < GT_R; ++kk) {
-            const f32x2 wk = tw.w[ch * GT_R + kk];
+        for (int kk = 0; kk < TC; ++kk) {
+            const f32x2 wk = tw.w[ch * TC + kk];
 #pragma unroll
             for (int r = 0; r < GT_R; ++r) acc[r] = fma2(win[r + kk], wk, acc[r]);
         }
 #pragma unroll
-        for (int i = 0; i < GT_R - 1; ++i) win[i] = win[GT_R + i];
+        for (int i = 0; i < GT_R - 1; ++i) win[i] = win[TC + i];
     }
 }
 
@@ -274,7 +275,7 @@ template <> struct StF<uint8_t, true> {
 };
 
 // Row pass: lane = row, warp item = (pixel blocks xb and xb + 4, channel): 16 outputs per thread.
-template <typename In, typename Mid, int C, bool Q15>
+template <typename In, typename Mid, int C, bool Q15, int TC>
 __global__ void __launch_bounds__(GT_THREADS)
 row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, size_t total_rows, int half,
                  int shift, int nch, int in_pitch, const __grid_constant__ TapWeights2 tw) {
@@ -284,7 +285,7 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int x0 = blockIdx.x * ROW_XT;
     const size_t row0 = (size_t)blockIdx.y * ROW_ROWS;
-    const int sp = ROW_XT + nch * GT_R - 1;
+    const int sp = ROW_XT + nch * TC - 1;
     const int row_elems = sp * C;
     const size_t g_pitch = (size_t)W * C;
     const int xs = x0 - half - shift;
@@ -320,7 +321,7 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
         if (item < ITEMS) {
             const int xb = item / C, c = item - xb * C;
             const float *a = s_in + lane * in_pitch + (xb * GT_R) * C + c;
-            conv8x2<C, false>(a, a + HALF_BLOCKS * GT_R * C, nch, tw, acc[it]);
+            conv8x2<C, false, TC>(a, a + HALF_BLOCKS * GT_R * C, nch, tw, acc[it]);
         }
     }
     __syncthreads();
@@ -349,7 +350,7 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
 }
 
 // Column pass: thread = two adjacent subpixel columns x 8 rows; one LDS.64 per staged row.
-template <typename Mid, typename Out, bool Q15>
+template <typename Mid, typename Out, bool Q15, int TC>
 __global__ void __launch_bounds__(GT_THREADS)
 col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
                  int nch, int zero_first_row, const __grid_constant__ TapWeights2 tw) {
@@ -359,7 +360,7 @@ col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
     const uint32_t s0 = blockIdx.x * COL_TW;
     const uint32_t img = blockIdx.y / tiles_y;
     const int y0 = (int)(blockIdx.y % tiles_y) * COL_TH;
-    const int sr = COL_TH + nch * GT_R - 1;
+    const int sr = COL_TH + nch * TC - 1;
     const Mid *m = mid + (size_t)img * H * row_sub;
 
     // stage [sr][COL_TW] with clamped rows; 16-byte async copies when the rows allow it
@@ -390,7 +391,7 @@ col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) acc[r] = 0ull;
         const float *a = s + (rb * GT_R) * COL_TW + 2 * cp;
-        conv8x2<COL_TW, true>(a, a + 1, nch, tw, acc);
+        conv8x2<COL_TW, true, TC>(a, a + 1, nch, tw, acc);
         const uint32_t col = s0 + 2 * cp;
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) {
@@ -415,19 +416,30 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
                     cudaStream_t st) {
     // Q0.15 on u8: exact in f32 (see StF), so it rides the FFMA2 kernels with integer-valued weights
     constexpr bool Q15F = std::is_same<Acc, uint32_t>::value && std::is_same<T, uint8_t>::value;
-    const int rnch = (rlen + GT_R - 1) / GT_R, cnch = (clen + GT_R - 1) / GT_R;
+    constexpr bool F32X2 = std::is_same<Acc, float>::value || Q15F;
+    // taps per unrolled chunk: the FFMA2 kernels pick the chunk size with the least zero padding
+    auto best_tc = [](int len) {
+        int best = GT_R, waste = (len + GT_R - 1) / GT_R * GT_R - len;
+        for (int tc = GT_R - 1; tc >= 5; --tc) {
+            const int w_ = (len + tc - 1) / tc * tc - len;
+            if (w_ < waste) { waste = w_; best = tc; }
+        }
+        return best;
+    };
+    const int rtc = F32X2 ? best_tc(rlen) : GT_R, ctc = F32X2 ? best_tc(clen) : GT_R;
+    const int rnch = (rlen + rtc - 1) / rtc, cnch = (clen + ctc - 1) / ctc;
     const size_t total_rows = (size_t)h * n_images;
     const uint32_t row_sub = w * (uint32_t)C;
     const int tiles_y = (int)((h + COL_TH - 1) / COL_TH);
-    const int sp = ROW_XT + rnch * GT_R - 1;
+    const int sp = ROW_XT + rnch * rtc - 1;
     const int in_pitch = (sp * C + 4) | 1, out_pitch = (ROW_XT * C) | 1;
     const size_t row_smem_int = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
     const size_t row_smem = (size_t)ROW_ROWS * std::max(in_pitch, out_pitch) * 4;  // f32 kernels alias the two
-    const size_t col_smem = (size_t)(COL_TH + cnch * GT_R - 1) * COL_TW * 4;
+    const size_t col_smem = (size_t)(COL_TH + cnch * ctc - 1) * COL_TW * 4;
     const dim3 row_grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
     const dim3 col_grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
 
-    if constexpr (std::is_same<Acc, float>::value || Q15F) {
+    if constexpr (F32X2) {
         TapWeights2 rwl, cwl;
         for (int i = 0; i < GT_MAX_TAPS; ++i) {
             uint32_t a = i < rlen ? rk[i] : 0u, b = i < clen ? ck[i] : 0u;
@@ -439,11 +451,18 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
             rwl.w[i] = ((f32x2)a << 32) | a;
             cwl.w[i] = ((f32x2)b << 32) | b;
         }
-#define ROW_GO(CC)                                                                                                   \
+#define ROW_GO2(CC, TCC)                                                                                             \
     {                                                                                                                \
-        auto k = row_f32x2_kernel<T, Mid, CC, Q15F>;                                                                 \
+        auto k = row_f32x2_kernel<T, Mid, CC, Q15F, TCC>;                                                            \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem));              \
         k<<<row_grid, GT_THREADS, row_smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rwl); \
+    }
+#define ROW_GO(CC)                                                                                                   \
+    switch (rtc) {                                                                                                   \
+        case 5: ROW_GO2(CC, 5) break;                                                                                \
+        case 6: ROW_GO2(CC, 6) break;                                                                                \
+        case 7: ROW_GO2(CC, 7) break;                                                                                \
+        default: ROW_GO2(CC, 8) break;                                                                               \
     }
         switch (C) {
             case 1: ROW_GO(1) break;
@@ -452,9 +471,20 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
             default: ROW_GO(4) break;
         }
 #undef ROW_GO
-        auto k = col_f32x2_kernel<Mid, T, Q15F>;
-        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));
-        k<<<col_grid, GT_THREADS, col_smem, st>>>((const Mid *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl);
+#undef ROW_GO2
+#define COL_GO(TCC)                                                                                                  \
+    {                                                                                                                \
+        auto k = col_f32x2_kernel<Mid, T, Q15F, TCC>;                                                                \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));              \
+        k<<<col_grid, GT_THREADS, col_smem, st>>>((const Mid *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl); \
+    }
+        switch (ctc) {
+            case 5: COL_GO(5) break;
+            case 6: COL_GO(6) break;
+            case 7: COL_GO(7) break;
+            default: COL_GO(8) break;
+        }
+#undef COL_GO
     } else {
         TapWeights rw, cw;
         for (int i = 0; i < GT_MAX_TAPS; ++i) { rw.w[i] = i < rlen ? rk[i] : 0u; cw.w[i] = i < clen ? ck[i] : 0u; }
