@@ -110,22 +110,26 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
     const int tw = min(H_XT, W - x0);
     const int sp = tw + 2 * r;                           // staged pixels (clamped at the image edges)
     const int sbytes = sp * C;
-    const int swords = (sbytes + 3) / 4;
     const size_t g_pitch = (size_t)W * C;                // bytes; multiple of 4 (checked by the host)
     const bool interior = x0 - r >= 0 && x0 + tw + r <= W;
 
+    // Interior tiles are staged with asynchronous 4-byte copies of the ALIGNED global words (every
+    // copy of the tile in flight at once); the rows' byte phase -- the same for all rows, the pitch
+    // being a multiple of 4 -- is taken out by funnel shifts when the words are used.
+    int phase = 0;
+    if (interior) {
+        const uint8_t *gb0 = src + (size_t)(x0 - r) * C;
+        phase = (int)(reinterpret_cast<uintptr_t>(gb0) & 3);
+    }
+    const int swords = (phase + sbytes + 3) / 4;
     for (int rr = warp; rr < H_ROWS; rr += H_THREADS / 32) {
         const uint8_t *grow = src + min(row0 + rr, total_rows - 1) * g_pitch;
         uint32_t *s = s_in + (size_t)rr * in_pitch;
         if (interior) {
-            // word-aligned in shared memory whatever the global phase: funnel two aligned global words
-            const uint8_t *gb = grow + (size_t)(x0 - r) * C;
-            const int phase = (int)(reinterpret_cast<uintptr_t>(gb) & 3);
-            const uint32_t *gw = reinterpret_cast<const uint32_t *>(gb - phase);
+            const uint32_t *gw = reinterpret_cast<const uint32_t *>(grow + (size_t)(x0 - r) * C - phase);
             for (int wi = lane; wi < swords; wi += 32) {
-                const uint32_t lo = __ldg(gw + wi);
-                const uint32_t hi = (phase && 4 * (wi + 1) < phase + sbytes) ? __ldg(gw + wi + 1) : 0u;
-                s[wi] = __funnelshift_r(lo, hi, phase * 8);
+                const uint32_t d = (uint32_t)__cvta_generic_to_shared(s + wi);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gw + wi) : "memory");
             }
         } else {
             uint8_t *sb = reinterpret_cast<uint8_t *>(s);
@@ -135,35 +139,38 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
             }
         }
     }
+    asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
     // lane = row; item = 64-pixel chunk; steps of 4 pixels = C words
     const int chunks = (tw + H_XC - 1) / H_XC;
     const uint32_t *in_row = s_in + (size_t)lane * in_pitch;
     uint32_t *out_row = s_out + (size_t)lane * out_pitch;
-    const int nshift = ((2 * r + 1) * C) & 3;  // byte misalignment of the incoming pixels relative to the outgoing ones
+    const int pshift = phase * 8;                                // outgoing pixels: byte phase of the staged row
+    const int nbyte = ((2 * r + 1) * C + phase) & 3;             // incoming pixels: phase + window offset
     for (int ck = warp; ck < chunks; ck += H_THREADS / 32) {
         const int xa = ck * H_XC, xb = min(xa + H_XC, tw);
         uint32_t sum[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) sum[c] = g.bias;
         {
-            const uint8_t *b = reinterpret_cast<const uint8_t *>(in_row) + xa * C;
+            const uint8_t *b = reinterpret_cast<const uint8_t *>(in_row) + phase + xa * C;
             for (int j = 0; j <= 2 * r; ++j) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) sum[c] += b[j * C + c];
             }
         }
-        const uint32_t *pw = in_row + (xa * C) / 4;                        // outgoing pixels: word aligned (xa % 4 == 0)
-        const uint32_t *nw = in_row + ((xa + 2 * r + 1) * C) / 4;          // incoming pixels: aligned down; shifted by nshift bytes
+        const uint32_t *pw = in_row + (xa * C + phase) / 4;                    // outgoing pixels, aligned down
+        const uint32_t *nw = in_row + ((xa + 2 * r + 1) * C + phase) / 4;      // incoming pixels, aligned down
         for (int x = xa; x < xb; x += 4) {
-            uint32_t prev[C], next[C], nraw[C + 1], outw[C];
+            uint32_t prev[C], next[C], praw[C + 1], nraw[C + 1], outw[C];
 #pragma unroll
-            for (int k = 0; k < C; ++k) prev[k] = pw[k];
+            for (int k = 0; k <= C; ++k) { praw[k] = pw[k]; nraw[k] = nw[k]; }
 #pragma unroll
-            for (int k = 0; k <= C; ++k) nraw[k] = nw[k];
-#pragma unroll
-            for (int k = 0; k < C; ++k) next[k] = __funnelshift_r(nraw[k], nraw[k + 1], nshift * 8);
+            for (int k = 0; k < C; ++k) {
+                prev[k] = __funnelshift_r(praw[k], praw[k + 1], pshift);
+                next[k] = __funnelshift_r(nraw[k], nraw[k + 1], nbyte * 8);
+            }
             uint32_t ob[4 * C];
 #pragma unroll
             for (int b = 0; b < 4 * C; ++b) {
