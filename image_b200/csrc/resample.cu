@@ -50,6 +50,7 @@ struct ResizeArgs {
     int max_cols, max_rows;     // bound of the staged source region (pixels, rows)
     int src_pitch;              // bytes per staged source row
     int tmp_pitch;              // floats per intermediate row
+    int out_pitch;              // subpixels per staged output row
 };
 
 // One CTA = one TW x TH tile of the destination of one image (grid: x = tile column, y = tile
@@ -143,7 +144,26 @@ resize_kernel(const ResizeArgs a) {
     __syncthreads();
 
     // ---- vertical pass: s_tmp[oyl][s] = acc_init + sum_i src[vleft+i][s] * vw[i] ----
-    {
+    if (sizeof(T) == 4 && !STRICT && row_bytes % 16 == 0) {
+        // f32 pixels: four subpixels per thread and tap (LDS.128 + 2 FFMA2)
+        const int quads = row_bytes / 16;
+        const f32x2 init2 = pack2(a.acc_init, a.acc_init);
+        for (int idx = tid; idx < th * quads; idx += THREADS) {
+            const int oyl = idx / quads, q = idx - oyl * quads;
+            const int l = a.vleft[oy0 + oyl] - row0, n = a.vcount[oy0 + oyl];
+            const float2 *wv = s_vw + oyl * a.vstride;
+            const unsigned char *p = s_src + (size_t)l * a.src_pitch + q * 16;
+            f32x2 a01 = init2, a23 = init2;
+            for (int i = 0; i < n; ++i) {
+                const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p);
+                const f32x2 ww = *reinterpret_cast<const f32x2 *>(wv + i);
+                a01 = fma2(v.x, ww, a01);
+                a23 = fma2(v.y, ww, a23);
+                p += a.src_pitch;
+            }
+            *reinterpret_cast<ulonglong2 *>(s_tmp + (size_t)oyl * a.tmp_pitch + q * 4) = make_ulonglong2(a01, a23);
+        }
+    } else {
         constexpr int N = Word<T>::N;
         const int words = (row_sub + N - 1) / N;
         const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
@@ -193,9 +213,14 @@ resize_kernel(const ResizeArgs a) {
     }
     __syncthreads();
 
-    // ---- horizontal pass out of s_tmp; results staged in s_src (now free) ----
+    // ---- horizontal pass out of s_tmp.  Results are staged in s_src (now free) and stored row-wise,
+    // except 16-byte pixels (f32 x 4): a warp's 8-row x 4-column patch already writes full 64-byte
+    // runs, so those go straight to global memory. ----
+    constexpr bool DIRECT = sizeof(T) * C == 16;
     T *s_out = reinterpret_cast<T *>(s_src);
-    const int out_pitch = a.TW * C;  // subpixels per staged output row
+    const int out_pitch = a.out_pitch;  // subpixels per staged output row: 16-byte multiple, odd number of 16-byte units
+    const size_t d_pitch = (size_t)a.nw * C;
+    T *g0 = dst + (size_t)(oy0 - (int)a.dst_row0) * d_pitch + (size_t)ox0 * C;
     {
         const int items = a.TW * a.TH;  // lane = 8 rows x 4 columns: distinct banks for the float4 reads
         for (int e = tid; e < items; e += THREADS) {
@@ -234,20 +259,30 @@ resize_kernel(const ResizeArgs a) {
                     t += C;
                 }
             }
-            T *o = s_out + (size_t)oyl * out_pitch + oxl * C;
+            if constexpr (DIRECT) {
+                T *o = g0 + (size_t)oyl * d_pitch + oxl * C;
+                T r[C];
 #pragma unroll
-            for (int c = 0; c < C; ++c) o[c] = Px<T>::clamp_nearest(acc[c]);
+                for (int c = 0; c < C; ++c) r[c] = Px<T>::clamp_nearest(acc[c]);
+                if ((reinterpret_cast<uintptr_t>(o) & 15) == 0) *reinterpret_cast<uint4 *>(o) = *reinterpret_cast<const uint4 *>(r);
+                else {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) o[c] = r[c];
+                }
+            } else {
+                T *o = s_out + (size_t)oyl * out_pitch + oxl * C;
+#pragma unroll
+                for (int c = 0; c < C; ++c) o[c] = Px<T>::clamp_nearest(acc[c]);
+            }
         }
     }
+    if constexpr (DIRECT) return;
     __syncthreads();
 
     // ---- store the tile, row-wise coalesced ----
     {
-        const size_t d_pitch = (size_t)a.nw * C;
-        T *g0 = dst + (size_t)(oy0 - (int)a.dst_row0) * d_pitch + (size_t)ox0 * C;
         const int sub = tw * C;
-        const bool vec_ok = (sizeof(T) * d_pitch) % 16 == 0 && (reinterpret_cast<uintptr_t>(g0) & 15) == 0 &&
-                            (sizeof(T) * sub) % 16 == 0 && (sizeof(T) * out_pitch) % 16 == 0;
+        const bool vec_ok = (sizeof(T) * d_pitch) % 16 == 0 && (reinterpret_cast<uintptr_t>(g0) & 15) == 0 && (sizeof(T) * sub) % 16 == 0;
         const int lane = tid & 31;
         if (vec_ok) {
             const int v_per_row = (int)(sizeof(T) * sub / 16);
@@ -321,7 +356,7 @@ int max_extent(const AxisTable &t, uint32_t first, uint32_t count, int tile) {
     return m;
 }
 
-struct Plan { int TW, TH, max_cols, max_rows, src_pitch, tmp_pitch; size_t smem; };
+struct Plan { int TW, TH, max_cols, max_rows, src_pitch, tmp_pitch, out_pitch; size_t smem; };
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
@@ -340,14 +375,18 @@ bool plan_tiles(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             p.TW = TW; p.TH = TH;
             p.max_cols = max_extent(ht, 0, nw, TW);
             p.max_rows = max_extent(vt, dst_row0, dst_rows, TH);
-            const int out_bytes_row = TW * C * tsize;
+            // staged output rows: a 16-byte multiple with an odd number of 16-byte units, so the 8 rows a
+            // warp writes in the horizontal pass fall into different bank groups
+            int out_bytes_row = round_up(TW * C * tsize, 16);
+            if ((out_bytes_row / 16) % 2 == 0) out_bytes_row += 16;
+            p.out_pitch = out_bytes_row / tsize;
+            const bool direct = C * tsize == 16;  // f32 x 4: no output staging
             // +32: the span may be widened to 16-byte boundaries on both sides
-            p.src_pitch = round_up(std::max(p.max_cols * C * tsize + 32, out_bytes_row), 16);
+            p.src_pitch = round_up(p.max_cols * C * tsize + 32, 16);
             int tp = round_up(p.src_pitch / tsize, 4);
             if ((tp / 4) % 2 == 0) tp += 4;  // odd number of 16-byte units: the 8-row lane pattern hits 8 bank groups
             p.tmp_pitch = tp;
-            const int src_rows_needed = std::max(p.max_rows, (TH * out_bytes_row + p.src_pitch - 1) / p.src_pitch);
-            p.max_rows = src_rows_needed;
+            if (!direct) p.max_rows = std::max(p.max_rows, (TH * out_bytes_row + p.src_pitch - 1) / p.src_pitch);
             p.smem = (size_t)p.max_rows * p.src_pitch + (size_t)TH * p.tmp_pitch * 4 + (size_t)TH * vt.stride * 8 +
                      (size_t)TW * ht.stride * 8 + (size_t)TW * 4 + 128;
             if (p.smem > smem_budget) continue;
@@ -538,7 +577,7 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     a.TW = p.TW; a.TH = p.TH;
     a.tiles_x = (int)((nw + p.TW - 1) / p.TW);
     a.tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
-    a.max_cols = p.max_cols; a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.tmp_pitch = p.tmp_pitch;
+    a.max_cols = p.max_cols; a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.tmp_pitch = p.tmp_pitch; a.out_pitch = p.out_pitch;
     if (a.tiles_y > 65535 || n_images > 65535) return fail(B200IMG_ERR_DIMENSION, "resize: too many tiles / images for one launch");
     const dim3 grid((unsigned)a.tiles_x, (unsigned)a.tiles_y, n_images);
     switch (dtype) {
