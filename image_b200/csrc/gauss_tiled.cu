@@ -426,7 +426,9 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
         }
         return best;
     };
-    const int rtc = F32X2 ? best_tc(rlen) : GT_R, ctc = F32X2 ? best_tc(clen) : GT_R;
+    // Measured on B200 (65 and 21 taps): the row pass is fastest with the least padding (13 x 5, 3 x 7),
+    // the column pass with 8-tap chunks even when that pads (fewer, longer unrolled bodies).
+    const int rtc = F32X2 ? best_tc(rlen) : GT_R, ctc = GT_R;
     const int rnch = (rlen + rtc - 1) / rtc, cnch = (clen + ctc - 1) / ctc;
     const size_t total_rows = (size_t)h * n_images;
     const uint32_t row_sub = w * (uint32_t)C;
