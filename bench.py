@@ -205,9 +205,9 @@ def run_b200(args):
                      "frac": round(achieved / hbm, 4), "traffic": traffic, "peak_source": hbm_src,
                      "kernel": "gaussian row+column passes of one batch call",
                      "algorithmic_bytes_per_launch": alg_bytes,
-                     "fp32_bound": {"fma_per_step": 2 * 72 * BATCH * W4K * H4K * 3, "peak_tfma_s": 35.9,
-                                    "frac": round(2 * 72 * BATCH * W4K * H4K * 3 / 35.9e12 / (ms / 1e3), 4),
-                                    "note": "65 taps (72 padded) x 2 passes per subpixel on the FP32 pipes; peak = FFMA rate "
+                     "fp32_bound": {"fma_per_step": (65 + 72) * BATCH * W4K * H4K * 3, "peak_tfma_s": 35.9,
+                                    "frac": round((65 + 72) * BATCH * W4K * H4K * 3 / 35.9e12 / (ms / 1e3), 4),
+                                    "note": "65 taps in the row pass + 72 (padded) in the column pass per subpixel on the FP32 pipes; peak = FFMA rate "
                                             "measured with tools/micro/ffma2.cu"},
                      "note": "traffic = both kernels of the call (f32 intermediate written and re-read); the op is "
                              "FP32-pipe bound, see DESIGN.md section 5"},
