@@ -55,8 +55,11 @@ def _compile(src: str, force: bool) -> str:
 
 
 def build(force: bool = False) -> str:
-    os.makedirs(OBJ, exist_ok=True)
     srcs = _sources()
+    deps = [os.path.join(CSRC, f) for f in srcs] + _headers()
+    if not force and os.path.exists(SO) and all(os.path.getmtime(d) <= os.path.getmtime(SO) for d in deps):
+        return SO  # up to date (the object directory need not exist: it does not travel to the GPU box)
+    os.makedirs(OBJ, exist_ok=True)
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(lambda s: _compile(s, force), srcs))
     if force or not os.path.exists(SO) or any(os.path.getmtime(o) > os.path.getmtime(SO) for o in objs):
