@@ -74,6 +74,10 @@ SIGNATURES = {
     "b200img_fast_blur_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f]),
     "b200img_fast_blur_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f, _vp]),
     "b200img_fast_blur_noalloc_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
+    "b200img_filter3x3": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp]),
+    "b200img_filter3x3_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp, _vp]),
+    "b200img_unsharpen": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i]),
+    "b200img_unsharpen_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i, _vp]),
     "b200img_convert": (_i, [_vp, _i, _i, _vp, _i, _i, _sz, _i, _vp]),
     "b200img_convert_dev": (_i, [_vp, _i, _i, _vp, _i, _i, _sz, _i, _vp, _vp]),
     "b200img_swizzle_02": (_i, [_vp, _i, _i, _sz]),

@@ -28,6 +28,10 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
                          const b200img_gauss_params *p, int path, int flags, cudaStream_t st);
 int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      float sigma, cudaStream_t st);
+int filter3x3_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
+                     const float kernel[9], cudaStream_t st);
+int unsharpen_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images, float sigma,
+                     int threshold, int flags, cudaStream_t st);
 
 // ---- errors -------------------------------------------------------------------
 static thread_local char g_err[512] = "";
@@ -503,6 +507,61 @@ int b200img_fast_blur(const void *src, uint32_t w, uint32_t h, int C, int dtype,
     if ((rc = hc.in(src, bytes, &ds))) return rc;
     if ((rc = hc.out_buf(bytes, &dd))) return rc;
     if ((rc = fast_blur_launch(ds, w, h, C, dtype, dd, 1, sigma, 0))) return rc;
+    return hc.out(dst, dd, bytes);
+}
+
+// ---- filter3x3 / unsharpen ---------------------------------------------
+int b200img_filter3x3_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, const float kernel[9], void *stream) {
+    size_t bytes;
+    int rc = check_image("filter3x3", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (!kernel) return fail(B200IMG_ERR_BAD_ARG, "filter3x3: null kernel");
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "filter3x3: null buffer");
+    return filter3x3_launch(src, w, h, C, dtype, dst, 1, kernel, (cudaStream_t)stream);
+}
+
+int b200img_filter3x3(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, const float kernel[9]) {
+    size_t bytes;
+    int rc = check_image("filter3x3", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (!kernel) return fail(B200IMG_ERR_BAD_ARG, "filter3x3: null kernel");
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "filter3x3: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    if ((rc = hc.out_buf(bytes, &dd))) return rc;
+    if ((rc = filter3x3_launch(ds, w, h, C, dtype, dd, 1, kernel, 0))) return rc;
+    return hc.out(dst, dd, bytes);
+}
+
+int b200img_unsharpen_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float sigma, int threshold,
+                          int flags, void *stream) {
+    size_t bytes;
+    int rc = check_image("unsharpen", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    b200img_gauss_params p;
+    if (gauss_params_from_sigma(sigma, &p)) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: sigma must be non-negative and finite");
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: null buffer");
+    set_scratch_stream((cudaStream_t)stream);
+    return unsharpen_launch(src, w, h, C, dtype, dst, 1, sigma, threshold, flags, (cudaStream_t)stream);
+}
+
+int b200img_unsharpen(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float sigma, int threshold, int flags) {
+    size_t bytes;
+    int rc = check_image("unsharpen", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    b200img_gauss_params p;
+    if (gauss_params_from_sigma(sigma, &p)) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: sigma must be non-negative and finite");
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    if ((rc = hc.out_buf(bytes, &dd))) return rc;
+    if ((rc = unsharpen_launch(ds, w, h, C, dtype, dd, 1, sigma, threshold, flags, 0))) return rc;
     return hc.out(dst, dd, bytes);
 }
 

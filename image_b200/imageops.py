@@ -242,6 +242,34 @@ def fast_blur(image, sigma: float):
     return out
 
 
+def filter3x3(image, kernel):
+    """imageops::filter3x3 (src/imageops/sample.rs:897): `kernel` = 9 weights, row-major."""
+    im = _Img(image)
+    out = im.empty_like()
+    k = (C.c_float * 9)(*[float(v) for v in np.asarray(kernel, np.float32).reshape(9)])
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(lib.b200img_filter3x3_dev, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), C.cast(k, C.c_void_p), _stream(im.a))
+    else:
+        _call(lib.b200img_filter3x3, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), C.cast(k, C.c_void_p))
+    return out
+
+
+def unsharpen(image, sigma: float, threshold: int, *, flags: int = L.FP_FAST):
+    """imageops::unsharpen (src/imageops/sample.rs:1617)."""
+    im = _Img(image)
+    out = im.empty_like()
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(lib.b200img_unsharpen_dev, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), float(sigma), int(threshold), flags,
+                  _stream(im.a))
+    else:
+        _call(lib.b200img_unsharpen, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), float(sigma), int(threshold), flags)
+    return out
+
+
 def convert_pixels(image, dst_channels: int, dst_dtype, *, mode: int = L.CAST, coefs=None):
     """Pixel-format conversion of a (h, w, c) / (n, c) array: mode CAST = DynamicImage::to_*,
     mode CONVERT = ImageBuffer::convert."""

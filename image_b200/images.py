@@ -167,3 +167,11 @@ class DynamicImage:
 
     def fast_blur(self, sigma: float) -> "DynamicImage":
         return DynamicImage(ImageBuffer(imageops.fast_blur(self.buf.data, sigma)), self.luma_coefs)
+
+    def unsharpen(self, sigma: float, threshold: int) -> "DynamicImage":
+        """DynamicImage::unsharpen (src/images/dynimage.rs:1277): imageops::unsharpen per variant."""
+        return DynamicImage(ImageBuffer(imageops.unsharpen(self.buf.data, sigma, threshold)), self.luma_coefs)
+
+    def filter3x3(self, kernel) -> "DynamicImage":
+        """DynamicImage::filter3x3 (src/images/dynimage.rs:1291)."""
+        return DynamicImage(ImageBuffer(imageops.filter3x3(self.buf.data, kernel)), self.luma_coefs)

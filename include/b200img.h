@@ -214,6 +214,21 @@ int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int c
 int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
                                   void *d_dst, float sigma, void *stream);
 
+/* ---- 3x3 filter and unsharp mask (the callers next to the core path) -------
+ * imageops::filter3x3, src/imageops/sample.rs:897-956: f32 accumulation in tap order, times
+ * 1/sum(kernel) (1 if the sum is 0), clamp to [0, max], truncating cast; the one-pixel border
+ * keeps the zero fill.  imageops::unsharpen, sample.rs:1617-1654: blur_advanced(new_from_sigma)
+ * then the integer rule |c - blurred| > threshold ? clamp(2c - blurred, 0, max) : c.
+ * `flags` are the Gaussian engine's (STRICT = bit-exact). */
+int b200img_filter3x3(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                      const float kernel[9]);
+int b200img_filter3x3_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                          const float kernel[9], void *stream);
+int b200img_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                      float sigma, int threshold, int flags);
+int b200img_unsharpen_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                          float sigma, int threshold, int flags, void *stream);
+
 /* ---- pixel-format conversions --------------------------------------------
  * mode CAST    = DynamicImage::to_* / into_* (src/images/dynimage.rs:320-568
  *                -> CicpRgb::cast_pixels src/metadata/cicp.rs:706-1033;

@@ -76,6 +76,8 @@ def lib():
         L.orc_u8_box_store.argtypes = [u32, u32]; L.orc_u8_box_store.restype = C.c_uint8
         L.orc_convert.argtypes = [vp, i, i, vp, i, i, sz, i, vp]
         L.orc_swizzle_02.argtypes = [vp, i, i, sz]
+        L.orc_filter3x3.argtypes = [vp, u32, u32, i, i, vp, vp]
+        L.orc_unsharpen.argtypes = [vp, u32, u32, i, i, vp, f, C.c_int32]
         pu32 = C.POINTER(u32)
         L.orc_resize_dimensions.argtypes = [u32, u32, u32, u32, i, pu32, pu32]
         L.orc_resize_dimensions.restype = None
@@ -236,3 +238,26 @@ def resize_dimensions(w, h, nw, nh, fill: bool):
     ow, oh = C.c_uint32(), C.c_uint32()
     lib().orc_resize_dimensions(w, h, nw, nh, int(fill), C.byref(ow), C.byref(oh))
     return ow.value, oh.value
+
+
+def filter3x3(img, kernel):
+    """imageops::filter3x3 (src/imageops/sample.rs:897)."""
+    a = _img(img)
+    h, w, c = a.shape
+    k = np.ascontiguousarray(kernel, np.float32).reshape(9)
+    out = np.zeros_like(a)
+    rc = lib().orc_filter3x3(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), _ptr(k))
+    if rc:
+        raise RuntimeError(f"orc_filter3x3 rc={rc}")
+    return out
+
+
+def unsharpen(img, sigma: float, threshold: int):
+    """imageops::unsharpen (src/imageops/sample.rs:1617)."""
+    a = _img(img)
+    h, w, c = a.shape
+    out = np.zeros_like(a)
+    rc = lib().orc_unsharpen(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), float(sigma), int(threshold))
+    if rc:
+        raise RuntimeError(f"orc_unsharpen rc={rc}")
+    return out

@@ -88,6 +88,12 @@ int orc_convert(const void *src, int src_dtype, int src_channels, void *dst,
                 const float coefs[3]);
 int orc_swizzle_02(void *buf, int dtype, int channels, size_t nsubpixels);
 
+/* ---- "next" rows of SURVEY 8(f): filter3x3 (sample.rs:897-956), unsharpen (1617-1654) ---- */
+int orc_filter3x3(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                  const float kernel[9]);
+int orc_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                  float sigma, int32_t threshold);
+
 /* ---- host helper (src/math/utils.rs:56-84) ------------------------------ */
 void orc_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill,
                            uint32_t *ow, uint32_t *oh);

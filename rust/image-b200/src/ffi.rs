@@ -81,6 +81,15 @@ extern "C" {
     pub fn b200img_fast_blur_noalloc_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,
                                          dst: *mut c_void, sigma: c_float, stream: Stream) -> c_int;
 
+    pub fn b200img_filter3x3(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                             kernel: *const c_float) -> c_int;
+    pub fn b200img_filter3x3_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                 kernel: *const c_float, stream: Stream) -> c_int;
+    pub fn b200img_unsharpen(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                             sigma: c_float, threshold: c_int, flags: c_int) -> c_int;
+    pub fn b200img_unsharpen_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                 sigma: c_float, threshold: c_int, flags: c_int, stream: Stream) -> c_int;
+
     pub fn b200img_convert(src: *const c_void, src_dtype: c_int, src_channels: c_int, dst: *mut c_void, dst_dtype: c_int,
                            dst_channels: c_int, npixels: usize, mode: c_int, coefs: *const c_float) -> c_int;
     pub fn b200img_convert_dev(src: *const c_void, src_dtype: c_int, src_channels: c_int, dst: *mut c_void,

@@ -242,3 +242,43 @@ def test_swizzle():
     a = np.arange(14, dtype=U8)
     assert o.swizzle_02(a, 4).tolist() == [2, 1, 0, 3, 6, 5, 4, 7, 10, 9, 8, 11, 12, 13]
     assert o.swizzle_02(a, 3).tolist() == [2, 1, 0, 5, 4, 3, 8, 7, 6, 11, 10, 9, 12, 13]
+
+
+# ---- filter3x3 / unsharpen restatements (sample.rs:897-956, 1617-1654) -------------------
+def test_filter3x3_oracle_invariants():
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (9, 11, 3), dtype=np.uint8)
+    ident = o.filter3x3(img, [0, 0, 0, 0, 1, 0, 0, 0, 0])
+    assert np.array_equal(ident[1:-1, 1:-1], img[1:-1, 1:-1])
+    assert not ident[0].any() and not ident[-1].any() and not ident[:, 0].any() and not ident[:, -1].any()
+    # weights are normalised by their sum: a box kernel on a constant image gives the constant back
+    const = np.full((6, 7, 1), 77, np.uint8)
+    assert (o.filter3x3(const, [1] * 9)[1:-1, 1:-1] == 77).all()
+    # a zero-sum kernel is not normalised (inverse_sum = 1) and negative sums clamp to 0
+    edge = o.filter3x3(const, [1, 1, 1, 1, -8, 1, 1, 1, 1])
+    assert not edge.any()
+    # plain numpy restatement on f32, same tap order
+    f = rng.random((8, 9, 2), dtype=np.float32)
+    k = np.array([0.5, 1, 0.25, 2, 3, 1, 0.125, 1, 0.5], np.float32)
+    t = np.zeros((6, 7, 2), np.float32)
+    for j in range(3):
+        for i in range(3):
+            t = t + f[j:j + 6, i:i + 7] * k[j * 3 + i]
+    s = np.float32(0)
+    for v in k:
+        s = np.float32(s + v)
+    want = np.clip(t * (np.float32(1) / s), 0, 1).astype(np.float32)
+    assert np.array_equal(o.filter3x3(f, k)[1:-1, 1:-1], want)
+
+
+def test_unsharpen_oracle_invariants():
+    rng = np.random.default_rng(6)
+    const = np.full((12, 10, 3), 90, np.uint8)
+    assert np.array_equal(o.unsharpen(const, 2.0, 0), const)
+    img = rng.integers(0, 256, (14, 15, 3), dtype=np.uint8)
+    # a threshold nothing can exceed returns the image itself
+    assert np.array_equal(o.unsharpen(img, 1.5, 255), img)
+    blurred = o.gaussian_blur(img, o.gauss_params_from_sigma(1.5))
+    d = img.astype(np.int32) - blurred.astype(np.int32)
+    want = np.where(np.abs(d) > 3, np.clip(img.astype(np.int32) + d, 0, 255), img).astype(np.uint8)
+    assert np.array_equal(o.unsharpen(img, 1.5, 3), want)
