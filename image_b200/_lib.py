@@ -13,7 +13,7 @@ SO_PATH = os.path.join(_HERE, "lib", "libb200img.so")
 
 U8, U16, F32 = 0, 1, 2
 NEAREST, TRIANGLE, CATMULLROM, GAUSSIAN, LANCZOS3 = range(5)
-FP_FAST, FP_STRICT, FP_FUSED_MAC, RESIZE_UNFUSED, RESIZE_TILED = 0, 1, 2, 256, 512
+FP_FAST, FP_STRICT, FP_FUSED_MAC, RESIZE_UNFUSED, RESIZE_TILED, THUMBNAIL_PER_PIXEL = 0, 1, 2, 256, 512, 1024
 BLUR_GENERIC, BLUR_DYN = 0, 1
 CAST, CONVERT = 0, 1
 OK, ERR_BAD_ARG, ERR_DIMENSION, ERR_OOM, ERR_CUDA, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5
@@ -74,6 +74,9 @@ SIGNATURES = {
     "b200img_fast_blur_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f]),
     "b200img_fast_blur_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f, _vp]),
     "b200img_fast_blur_noalloc_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
+    "b200img_thumbnail": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i]),
+    "b200img_thumbnail_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i, _vp]),
+    "b200img_thumbnail_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _u32, _i, _vp]),
     "b200img_filter3x3": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp]),
     "b200img_filter3x3_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp, _vp]),
     "b200img_unsharpen": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i]),

@@ -28,6 +28,9 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
                          const b200img_gauss_params *p, int path, int flags, cudaStream_t st);
 int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      float sigma, cudaStream_t st);
+int thumbnail_check(uint32_t w, uint32_t h, int dtype, uint32_t nw, uint32_t nh);
+int thumbnail_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                     uint32_t n_images, int path, cudaStream_t st);
 int filter3x3_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      const float kernel[9], cudaStream_t st);
 int unsharpen_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images, float sigma,
@@ -508,6 +511,44 @@ int b200img_fast_blur(const void *src, uint32_t w, uint32_t h, int C, int dtype,
     if ((rc = hc.out_buf(bytes, &dd))) return rc;
     if ((rc = fast_blur_launch(ds, w, h, C, dtype, dd, 1, sigma, 0))) return rc;
     return hc.out(dst, dd, bytes);
+}
+
+// ---- thumbnail ------------------------------------------------------------
+static int thumbnail_front(uint32_t w, uint32_t h, int C, int dtype, uint32_t nw, uint32_t nh, size_t *sb, size_t *db) {
+    int rc = check_image("thumbnail", C, dtype, w, h, sb);
+    if (rc) return rc;
+    if ((rc = check_image("thumbnail", C, dtype, nw, nh, db))) return rc;
+    return thumbnail_check(w, h, dtype, nw, nh);
+}
+
+int b200img_thumbnail_batch_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                                uint32_t n_images, int flags, void *stream) {
+    size_t sb, db;
+    int rc = thumbnail_front(w, h, C, dtype, nw, nh, &sb, &db);
+    if (rc) return rc;
+    if (db == 0 || n_images == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "thumbnail: null buffer");
+    return thumbnail_launch(src, w, h, C, dtype, dst, nw, nh, n_images, (flags & B200IMG_THUMBNAIL_PER_PIXEL) ? 1 : 0,
+                            (cudaStream_t)stream);
+}
+
+int b200img_thumbnail_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
+                          int flags, void *stream) {
+    return b200img_thumbnail_batch_dev(src, w, h, C, dtype, dst, nw, nh, 1, flags, stream);
+}
+
+int b200img_thumbnail(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh, int flags) {
+    size_t sb, db;
+    int rc = thumbnail_front(w, h, C, dtype, nw, nh, &sb, &db);
+    if (rc) return rc;
+    if (db == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "thumbnail: null buffer");
+    HostCall hc;
+    void *ds, *dd;
+    if ((rc = hc.in(src, sb, &ds))) return rc;
+    if ((rc = hc.out_buf(db, &dd))) return rc;
+    if ((rc = thumbnail_launch(ds, w, h, C, dtype, dd, nw, nh, 1, (flags & B200IMG_THUMBNAIL_PER_PIXEL) ? 1 : 0, 0))) return rc;
+    return hc.out(dst, dd, db);
 }
 
 // ---- filter3x3 / unsharpen ---------------------------------------------

@@ -242,6 +242,30 @@ def fast_blur(image, sigma: float):
     return out
 
 
+def thumbnail(image, new_width: int, new_height: int, *, flags: int = 0):
+    """imageops::thumbnail (src/imageops/sample.rs:595).  A CUDA tensor of shape (n, h, w, c) is a batch."""
+    if _is_torch(image) and image.dim() == 4:
+        import torch
+        image = image.contiguous()
+        n, h, w, c = image.shape
+        dt = {torch.uint8: L.U8, torch.uint16: L.U16, torch.float32: L.F32}[image.dtype]
+        out = torch.zeros((n, new_height, new_width, c), dtype=image.dtype, device=image.device)
+        with torch.cuda.device(image.device):
+            _call(L.lib().b200img_thumbnail_batch_dev, image.data_ptr(), w, h, c, dt, out.data_ptr(), new_width, new_height,
+                  n, flags, _stream(image))
+        return out
+    im = _Img(image)
+    out = im.empty_like(h=new_height, w=new_width)
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(lib.b200img_thumbnail_dev, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), new_width, new_height, flags,
+                  _stream(im.a))
+    else:
+        _call(lib.b200img_thumbnail, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), new_width, new_height, flags)
+    return out
+
+
 def filter3x3(image, kernel):
     """imageops::filter3x3 (src/imageops/sample.rs:897): `kernel` = 9 weights, row-major."""
     im = _Img(image)

@@ -175,3 +175,12 @@ class DynamicImage:
     def filter3x3(self, kernel) -> "DynamicImage":
         """DynamicImage::filter3x3 (src/images/dynimage.rs:1291)."""
         return DynamicImage(ImageBuffer(imageops.filter3x3(self.buf.data, kernel)), self.luma_coefs)
+
+    def thumbnail_exact(self, nwidth: int, nheight: int) -> "DynamicImage":
+        """DynamicImage::thumbnail_exact (src/images/dynimage.rs:1175)."""
+        return DynamicImage(ImageBuffer(imageops.thumbnail(self.buf.data, nwidth, nheight)), self.luma_coefs)
+
+    def thumbnail(self, nwidth: int, nheight: int) -> "DynamicImage":
+        """DynamicImage::thumbnail (src/images/dynimage.rs:1159): aspect ratio kept, no fill."""
+        w2, h2 = imageops.resize_dimensions(self.width, self.height, nwidth, nheight, False)
+        return self.thumbnail_exact(w2, h2)

@@ -78,6 +78,9 @@ typedef enum {
 /* Resampler only: use the tile kernel even where the column-streaming kernel (downscales of
  * u8 / u16 images) applies.  Same results; exists so that both kernels can be tested. */
 #define B200IMG_RESIZE_TILED 512
+/* thumbnail only: evaluate every output pixel on its own (the kernel that serves upscales and
+ * unaligned rows) even where the column-sum kernel applies.  Same results; for tests. */
+#define B200IMG_THUMBNAIL_PER_PIXEL 1024
 
 const char *b200img_last_error(void);
 int b200img_version(void);
@@ -213,6 +216,22 @@ int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int c
  *     them on one stream or order them yourself. */
 int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
                                   void *d_dst, float sigma, void *stream);
+
+/* ---- thumbnail (the first caller next to the core path) --------------------
+ * imageops::thumbnail, src/imageops/sample.rs:564-886 (DynamicImage::thumbnail_exact,
+ * src/images/dynimage.rs:1175).  Integer images are bit-exact, including the reference's
+ * literal treatment of windows above 2^16 pixels (256x256 sub-block averages divided by
+ * (w/256)*(h/256)); f32 images sum in f64 and agree to f32 rounding.  An integer image whose
+ * window exceeds 2^16 pixels while being under 256 wide or high makes the reference divide
+ * by zero: B200IMG_ERR_BAD_ARG here. */
+int b200img_thumbnail(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                      uint32_t nw, uint32_t nh, int flags);
+int b200img_thumbnail_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                          void *d_dst, uint32_t nw, uint32_t nh, int flags, void *stream);
+/* n_images equally-shaped, tightly packed device images; one launch */
+int b200img_thumbnail_batch_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                                void *d_dst, uint32_t nw, uint32_t nh, uint32_t n_images, int flags,
+                                void *stream);
 
 /* ---- 3x3 filter and unsharp mask (the callers next to the core path) -------
  * imageops::filter3x3, src/imageops/sample.rs:897-956: f32 accumulation in tap order, times

@@ -78,6 +78,7 @@ def lib():
         L.orc_swizzle_02.argtypes = [vp, i, i, sz]
         L.orc_filter3x3.argtypes = [vp, u32, u32, i, i, vp, vp]
         L.orc_unsharpen.argtypes = [vp, u32, u32, i, i, vp, f, C.c_int32]
+        L.orc_thumbnail.argtypes = [vp, u32, u32, i, i, vp, u32, u32]
         pu32 = C.POINTER(u32)
         L.orc_resize_dimensions.argtypes = [u32, u32, u32, u32, i, pu32, pu32]
         L.orc_resize_dimensions.restype = None
@@ -260,4 +261,21 @@ def unsharpen(img, sigma: float, threshold: int):
     rc = lib().orc_unsharpen(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), float(sigma), int(threshold))
     if rc:
         raise RuntimeError(f"orc_unsharpen rc={rc}")
+    return out
+
+
+class ReferencePanic(RuntimeError):
+    """The reference panics on this input (integer division by zero in thumbnail_sample_block)."""
+
+
+def thumbnail(img, nw: int, nh: int):
+    """imageops::thumbnail (src/imageops/sample.rs:595)."""
+    a = _img(img)
+    h, w, c = a.shape
+    out = np.zeros((nh, nw, c), a.dtype)
+    rc = lib().orc_thumbnail(_ptr(a), w, h, c, _DT[a.dtype], _ptr(out), nw, nh)
+    if rc == -2:
+        raise ReferencePanic("thumbnail: block of > 65536 pixels under 256 wide or high")
+    if rc:
+        raise RuntimeError(f"orc_thumbnail rc={rc}")
     return out

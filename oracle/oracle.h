@@ -94,6 +94,10 @@ int orc_filter3x3(const void *src, uint32_t w, uint32_t h, int channels, int dty
 int orc_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
                   float sigma, int32_t threshold);
 
+/* imageops::thumbnail (sample.rs:564-886); -2 = the reference's integer division by zero */
+int orc_thumbnail(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                  uint32_t nw, uint32_t nh);
+
 /* ---- host helper (src/math/utils.rs:56-84) ------------------------------ */
 void orc_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill,
                            uint32_t *ow, uint32_t *oh);

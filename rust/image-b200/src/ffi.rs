@@ -81,6 +81,13 @@ extern "C" {
     pub fn b200img_fast_blur_noalloc_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,
                                          dst: *mut c_void, sigma: c_float, stream: Stream) -> c_int;
 
+    pub fn b200img_thumbnail(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                             nw: u32, nh: u32, flags: c_int) -> c_int;
+    pub fn b200img_thumbnail_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
+                                 nw: u32, nh: u32, flags: c_int, stream: Stream) -> c_int;
+    pub fn b200img_thumbnail_batch_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,
+                                       dst: *mut c_void, nw: u32, nh: u32, n_images: u32, flags: c_int,
+                                       stream: Stream) -> c_int;
     pub fn b200img_filter3x3(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                              kernel: *const c_float) -> c_int;
     pub fn b200img_filter3x3_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,

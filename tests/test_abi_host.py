@@ -122,3 +122,15 @@ def test_rust_ffi_declares_every_header_symbol():
     declared = set(re.findall(r"\b(b200img_[a-z0-9_]+)\s*\(", hdr))
     bound = set(re.findall(r"fn (b200img_[a-z0-9_]+)", rs))
     assert declared == bound, declared ^ bound
+
+
+def test_thumbnail_reference_panic_is_refused_without_a_gpu():
+    """thumbnail_sample_block divides by (w/256)*(h/256) = 0 (sample.rs:716,739): BAD_ARG before any CUDA call"""
+    lib = L.lib()
+    src = np.zeros((1000, 100, 1), np.uint8)
+    dst = np.zeros((1, 1, 1), np.uint8)
+    rc = lib.b200img_thumbnail(src.ctypes.data, 100, 1000, 1, L.U8, dst.ctypes.data, 1, 1, 0)
+    assert rc == L.ERR_BAD_ARG and "divides by zero" in L.last_error()
+    assert lib.b200img_thumbnail(src.ctypes.data, 100, 1000, 5, L.U8, dst.ctypes.data, 1, 1, 0) == L.ERR_BAD_ARG
+    # an empty destination is a no-op
+    assert lib.b200img_thumbnail(src.ctypes.data, 100, 1000, 1, L.U8, dst.ctypes.data, 0, 7, 0) == 0

@@ -282,3 +282,24 @@ def test_unsharpen_oracle_invariants():
     d = img.astype(np.int32) - blurred.astype(np.int32)
     want = np.where(np.abs(d) > 3, np.clip(img.astype(np.int32) + d, 0, 255), img).astype(np.uint8)
     assert np.array_equal(o.unsharpen(img, 1.5, 3), want)
+
+
+# ---- thumbnail restatement (sample.rs:564-886) -------------------------------------------
+def test_thumbnail_reference_kat_huge_block():
+    """sample.rs:1922-1930 `thumbnail_huge_block`: neither input may overflow or panic."""
+    assert o.thumbnail(np.full((4113, 4096, 1), 255, np.uint8), 1, 1)[0, 0, 0] == 255
+    assert o.thumbnail(np.full((1024, 1024, 1), 65535, np.uint16), 1, 1)[0, 0, 0] == 65535
+
+
+def test_thumbnail_oracle_invariants():
+    rng = np.random.default_rng(7)
+    img = rng.integers(0, 256, (40, 60, 3), dtype=np.uint8)
+    want = (img.reshape(20, 2, 30, 2, 3).astype(np.uint32).sum(axis=(1, 3)) + 2) // 4
+    assert np.array_equal(o.thumbnail(img, 30, 20), want)
+    assert np.array_equal(o.thumbnail(img, 60, 40), img)          # same size: 1x1 blocks
+    const = np.full((10, 10, 3), 77, np.uint8)
+    for size in ((20, 20), (13, 7), (3, 25), (10, 10)):           # all four window forms
+        assert (o.thumbnail(const, *size) == 77).all()
+    assert not o.thumbnail(np.zeros((0, 4, 1), np.uint8), 3, 3).any()
+    with pytest.raises(o.ReferencePanic):                         # integer division by a zero count
+        o.thumbnail(np.zeros((1000, 100, 1), np.uint8), 1, 1)

@@ -1,0 +1,50 @@
+"""CUDA-event timings of the section-8f operators (thumbnail, filter3x3, unsharpen) on 8 x 4K Rgb8.
+usage: time_ops.py [reps]   -- prints one line per case: ms per call and algorithmic GB/s (src + dst bytes)."""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from image_b200 import imageops
+from image_b200 import _lib as L
+
+reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+dev = torch.device("cuda:0")
+g = torch.Generator(device=dev).manual_seed(1)
+lib = L.lib()
+st = torch.cuda.current_stream().cuda_stream
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timed(fn, nbytes, label):
+    for _ in range(3):
+        fn()
+    tot = 0.0
+    for _ in range(reps):
+        flush.zero_()                      # 256 MiB write: evicts the 126 MB L2
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); b.synchronize()
+        tot += a.elapsed_time(b)
+    ms = tot / reps
+    print(f"{label:44s} {ms:8.3f} ms  {nbytes / ms / 1e6:8.1f} GB/s")
+
+
+n, w, h = 8, 3840, 2160
+for tdt, dt, name in ((torch.uint8, L.U8, "u8"), (torch.uint16, L.U16, "u16"), (torch.float32, L.F32, "f32")):
+    if tdt == torch.float32:
+        src = torch.rand((n, h, w, 3), device=dev, generator=g)
+    else:
+        src = torch.randint(0, 256, (n, h, w, 3), device=dev, generator=g).to(tdt)
+    es = src.element_size()
+    for nw, nh in ((256, 256), (384, 216), (1920, 1080), (3000, 2000)):
+        dst = torch.empty((n, nh, nw, 3), dtype=tdt, device=dev)
+        for flags, tag in ((0, ""), (L.THUMBNAIL_PER_PIXEL, " per-pixel")):
+            fn = lambda: L.check(lib.b200img_thumbnail_batch_dev(src.data_ptr(), w, h, 3, dt, dst.data_ptr(), nw, nh, n, flags, st))
+            timed(fn, src.numel() * es + dst.numel() * es, f"thumbnail {name} 8x4K -> {nw}x{nh}{tag}")
+    if name != "u16":
+        small = src[:, :540, :960].contiguous()
+        dst = torch.empty((n, 2160, 3840, 3), dtype=tdt, device=dev)
+        fn = lambda: L.check(lib.b200img_thumbnail_batch_dev(small.data_ptr(), 960, 540, 3, dt, dst.data_ptr(), 3840, 2160, n, 0, st))
+        timed(fn, small.numel() * es + dst.numel() * es, f"thumbnail {name} 8x(960x540) -> 4K (upscale)")
+    one = src[0]
+    timed(lambda: imageops.filter3x3(one, [1, 1, 1, 1, -8, 1, 1, 1, 1]), 2 * one.numel() * es, f"filter3x3 {name} 4K")
+    timed(lambda: imageops.unsharpen(one, 2.0, 0), 2 * one.numel() * es, f"unsharpen {name} 4K sigma=2")
+    del src
