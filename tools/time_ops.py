@@ -1,12 +1,14 @@
 """CUDA-event timings of the section-8f operators (thumbnail, filter3x3, unsharpen) on 8 x 4K Rgb8.
-usage: time_ops.py [reps]   -- prints one line per case: ms per call and algorithmic GB/s (src + dst bytes)."""
+usage: time_ops.py [reps [label-regex]]   -- prints one line per case: ms per call and algorithmic GB/s (src + dst bytes)."""
 import os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from image_b200 import imageops
 from image_b200 import _lib as L
 
+import re
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+only = re.compile(sys.argv[2]) if len(sys.argv) > 2 else None
 dev = torch.device("cuda:0")
 g = torch.Generator(device=dev).manual_seed(1)
 lib = L.lib()
@@ -15,6 +17,8 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 
 def timed(fn, nbytes, label):
+    if only and not only.search(label):
+        return
     for _ in range(3):
         fn()
     tot = 0.0
