@@ -119,5 +119,31 @@ ImageBuffer<S, C> fast_blur(const ImageBuffer<S, C> &image, float sigma) {
     return out;
 }
 
+// imageops::thumbnail  src/imageops/sample.rs:595
+template <typename S, int C>
+ImageBuffer<S, C> thumbnail(const ImageBuffer<S, C> &image, uint32_t new_width, uint32_t new_height) {
+    ImageBuffer<S, C> out(new_width, new_height);
+    check(b200img_thumbnail(image.data.data(), image.width, image.height, C, SubpixelCode<S>::value, out.data.data(),
+                            new_width, new_height, 0));
+    return out;
+}
+
+// imageops::filter3x3  src/imageops/sample.rs:897
+template <typename S, int C>
+ImageBuffer<S, C> filter3x3(const ImageBuffer<S, C> &image, const float (&kernel)[9]) {
+    ImageBuffer<S, C> out(image.width, image.height);
+    check(b200img_filter3x3(image.data.data(), image.width, image.height, C, SubpixelCode<S>::value, out.data.data(), kernel));
+    return out;
+}
+
+// imageops::unsharpen  src/imageops/sample.rs:1617
+template <typename S, int C>
+ImageBuffer<S, C> unsharpen(const ImageBuffer<S, C> &image, float sigma, int32_t threshold, int flags = B200IMG_FP_FAST) {
+    ImageBuffer<S, C> out(image.width, image.height);
+    check(b200img_unsharpen(image.data.data(), image.width, image.height, C, SubpixelCode<S>::value, out.data.data(), sigma,
+                            threshold, flags));
+    return out;
+}
+
 }  // namespace imageops
 }  // namespace image_b200

@@ -120,6 +120,45 @@ pub mod imageops {
             <P::Subpixel as B200Subpixel>::DTYPE, out.as_mut_ptr() as *mut c_void, sigma) });
         out
     }
+
+    /// `image::imageops::thumbnail` (src/imageops/sample.rs:595).
+    pub fn thumbnail<I: GenericImageView>(image: &I, new_width: u32, new_height: u32)
+        -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    {
+        let src = packed(image);
+        let mut out = ImageBuffer::new(new_width, new_height);
+        check(unsafe { ffi::b200img_thumbnail(src.as_ptr() as *const c_void, image.width(), image.height(),
+            <I::Pixel as Pixel>::CHANNEL_COUNT as c_int, <<I::Pixel as Pixel>::Subpixel as B200Subpixel>::DTYPE,
+            out.as_mut_ptr() as *mut c_void, new_width, new_height, 0) });
+        out
+    }
+
+    /// `image::imageops::filter3x3` (src/imageops/sample.rs:897).
+    pub fn filter3x3<I: GenericImageView>(image: &I, kernel: &[f32; 9])
+        -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    {
+        let src = packed(image);
+        let mut out = ImageBuffer::new(image.width(), image.height());
+        check(unsafe { ffi::b200img_filter3x3(src.as_ptr() as *const c_void, image.width(), image.height(),
+            <I::Pixel as Pixel>::CHANNEL_COUNT as c_int, <<I::Pixel as Pixel>::Subpixel as B200Subpixel>::DTYPE,
+            out.as_mut_ptr() as *mut c_void, kernel.as_ptr()) });
+        out
+    }
+
+    /// `image::imageops::unsharpen` (src/imageops/sample.rs:1617).
+    pub fn unsharpen<I: GenericImageView>(image: &I, sigma: f32, threshold: i32)
+        -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    {
+        let src = packed(image);
+        let mut out = ImageBuffer::new(image.width(), image.height());
+        check(unsafe { ffi::b200img_unsharpen(src.as_ptr() as *const c_void, image.width(), image.height(),
+            <I::Pixel as Pixel>::CHANNEL_COUNT as c_int, <<I::Pixel as Pixel>::Subpixel as B200Subpixel>::DTYPE,
+            out.as_mut_ptr() as *mut c_void, sigma, threshold as c_int, ffi::FP_FAST) });
+        out
+    }
 }
 
 /// `ImageBuffer::convert::<To>()` (src/images/buffer.rs:1643): FromColor arithmetic.

@@ -56,6 +56,22 @@ int main() {
         (void)imageops::blur(img, 0.0f);
         EXPECT(imageops::fast_blur(ImageBuffer<uint8_t, 3>(0, 0), 3.0f).data.empty());
     }
+    {   // the widened operators: thumbnail_huge_block (sample.rs:1922), constant-image invariants
+        ImageBuffer<uint16_t, 1> huge(1024, 1024);
+        for (auto &v : huge.data) v = 65535;
+        EXPECT(imageops::thumbnail(huge, 1, 1).data[0] == 65535);
+        ImageBuffer<uint8_t, 3> img(60, 40);
+        for (auto &v : img.data) v = 90;
+        for (auto v : imageops::thumbnail(img, 17, 9).data) EXPECT(v == 90);
+        for (auto v : imageops::thumbnail(img, 100, 70).data) EXPECT(v == 90);
+        for (auto v : imageops::unsharpen(img, 2.0f, 0).data) EXPECT(v == 90);
+        const float box[9] = {1, 1, 1, 1, 1, 1, 1, 1, 1};
+        auto f = imageops::filter3x3(img, box);
+        EXPECT(f.data[(1 * 60 + 1) * 3] == 90 && f.data[0] == 0);   // interior averaged, border zero
+        bool threw = false;   // the reference divides by a zero count here
+        try { (void)imageops::thumbnail(ImageBuffer<uint8_t, 1>(100, 1000), 1, 1); } catch (const Panic &) { threw = true; }
+        EXPECT(threw);
+    }
     {   // panics of the reference surface as exceptions
         bool threw = false;
         try { GaussianBlurParameters::new_from_sigma(-1.0f); } catch (const Panic &) { threw = true; }
