@@ -81,6 +81,16 @@ SIGNATURES = {
     "b200img_filter3x3_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp, _vp]),
     "b200img_unsharpen": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i]),
     "b200img_unsharpen_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i, _vp]),
+    "b200img_invert": (_i, [_vp, _u32, _u32, _i, _i, _vp]),
+    "b200img_invert_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp]),
+    "b200img_brighten": (_i, [_vp, _u32, _u32, _i, _i, _vp, C.c_int32]),
+    "b200img_brighten_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, C.c_int32, _vp]),
+    "b200img_contrast": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f]),
+    "b200img_contrast_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
+    "b200img_huerotate": (_i, [_vp, _u32, _u32, _i, _i, _vp, C.c_int32]),
+    "b200img_huerotate_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, C.c_int32, _vp]),
+    "b200img_grayscale": (_i, [_vp, _u32, _u32, _i, _i, _vp, _i]),
+    "b200img_grayscale_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _i, _vp]),
     "b200img_convert": (_i, [_vp, _i, _i, _vp, _i, _i, _sz, _i, _vp]),
     "b200img_convert_dev": (_i, [_vp, _i, _i, _vp, _i, _i, _sz, _i, _vp, _vp]),
     "b200img_swizzle_02": (_i, [_vp, _i, _i, _sz]),

@@ -31,6 +31,8 @@ int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
 int thumbnail_check(uint32_t w, uint32_t h, int dtype, uint32_t nw, uint32_t nh);
 int thumbnail_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
                      uint32_t n_images, int path, cudaStream_t st);
+int colorop_launch(int op, const void *src, void *dst, size_t npixels, int C, int dtype, int32_t ivalue, float fvalue,
+                   cudaStream_t st);
 int filter3x3_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      const float kernel[9], cudaStream_t st);
 int unsharpen_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images, float sigma,
@@ -604,6 +606,69 @@ int b200img_unsharpen(const void *src, uint32_t w, uint32_t h, int C, int dtype,
     if ((rc = hc.out_buf(bytes, &dd))) return rc;
     if ((rc = unsharpen_launch(ds, w, h, C, dtype, dd, 1, sigma, threshold, flags, 0))) return rc;
     return hc.out(dst, dd, bytes);
+}
+
+// ---- colorops --------------------------------------------------------
+static int colorop_dev(const char *name, int op, const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                       int32_t ivalue, float fvalue, void *stream) {
+    size_t bytes;
+    int rc = check_image(name, C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "%s: null buffer", name);
+    return colorop_launch(op, src, dst, (size_t)w * h, C, dtype, ivalue, fvalue, (cudaStream_t)stream);
+}
+
+static int colorop_host(const char *name, int op, const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                        int32_t ivalue, float fvalue) {
+    size_t bytes;
+    int rc = check_image(name, C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0) return B200IMG_OK;
+    if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "%s: null buffer", name);
+    HostCall hc;
+    void *ds;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    if ((rc = colorop_launch(op, ds, ds, (size_t)w * h, C, dtype, ivalue, fvalue, 0))) return rc;  // in place on the device copy
+    return hc.out(dst, ds, bytes);
+}
+
+int b200img_invert(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst) {
+    return colorop_host("invert", 0, src, w, h, C, dtype, dst, 0, 0.0f);
+}
+int b200img_invert_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, void *stream) {
+    return colorop_dev("invert", 0, src, w, h, C, dtype, dst, 0, 0.0f, stream);
+}
+int b200img_brighten(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int32_t value) {
+    return colorop_host("brighten", 1, src, w, h, C, dtype, dst, value, 0.0f);
+}
+int b200img_brighten_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int32_t value, void *stream) {
+    return colorop_dev("brighten", 1, src, w, h, C, dtype, dst, value, 0.0f, stream);
+}
+int b200img_contrast(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float contrast) {
+    return colorop_host("contrast", 2, src, w, h, C, dtype, dst, 0, contrast);
+}
+int b200img_contrast_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, float contrast, void *stream) {
+    return colorop_dev("contrast", 2, src, w, h, C, dtype, dst, 0, contrast, stream);
+}
+int b200img_huerotate(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int32_t degrees) {
+    return colorop_host("huerotate", 3, src, w, h, C, dtype, dst, degrees, 0.0f);
+}
+int b200img_huerotate_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int32_t degrees, void *stream) {
+    return colorop_dev("huerotate", 3, src, w, h, C, dtype, dst, degrees, 0.0f, stream);
+}
+// grayscale / grayscale_alpha: pixel.to_luma() / to_luma_alpha() = FromColor in the source subpixel type
+int b200img_grayscale(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int keep_alpha) {
+    size_t bytes;
+    int rc = check_image("grayscale", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    return b200img_convert(src, dtype, C, dst, dtype, keep_alpha ? 2 : 1, (size_t)w * h, B200IMG_CONVERT, nullptr);
+}
+int b200img_grayscale_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, int keep_alpha, void *stream) {
+    size_t bytes;
+    int rc = check_image("grayscale", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    return b200img_convert_dev(src, dtype, C, dst, dtype, keep_alpha ? 2 : 1, (size_t)w * h, B200IMG_CONVERT, nullptr, stream);
 }
 
 // ---- conversions and swizzle ----------------------------------------------------

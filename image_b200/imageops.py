@@ -294,6 +294,68 @@ def unsharpen(image, sigma: float, threshold: int, *, flags: int = L.FP_FAST):
     return out
 
 
+def _colorop(name: str, image, *params, out=None):
+    im = _Img(image)
+    if out is None:
+        out = im.empty_like()
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(getattr(lib, f"b200img_{name}_dev"), im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), *params, _stream(im.a))
+    else:
+        _call(getattr(lib, f"b200img_{name}"), im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), *params)
+    return out
+
+
+def invert(image):
+    """imageops::invert (src/imageops/colorops.rs:70) -- IN PLACE, like the reference."""
+    return _colorop("invert", image, out=image)
+
+
+def brighten(image, value: int):
+    """imageops::brighten (colorops.rs:161)."""
+    return _colorop("brighten", image, int(value))
+
+
+def brighten_in_place(image, value: int):
+    return _colorop("brighten", image, int(value), out=image)
+
+
+def contrast(image, contrast: float):
+    """imageops::contrast (colorops.rs:92)."""
+    return _colorop("contrast", image, float(contrast))
+
+
+def contrast_in_place(image, contrast: float):
+    return _colorop("contrast", image, float(contrast), out=image)
+
+
+def huerotate(image, value: int):
+    """imageops::huerotate (colorops.rs:232); `value` in degrees."""
+    return _colorop("huerotate", image, int(value))
+
+
+def huerotate_in_place(image, value: int):
+    return _colorop("huerotate", image, int(value), out=image)
+
+
+def grayscale(image, *, alpha: bool = False):
+    """imageops::grayscale / grayscale_alpha (colorops.rs:14-25)."""
+    im = _Img(image)
+    out = im.empty_like(c=2 if alpha else 1)
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(lib.b200img_grayscale_dev, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), int(alpha), _stream(im.a))
+    else:
+        _call(lib.b200img_grayscale, im.ptr, im.w, im.h, im.c, im.dt, _ptr(out), int(alpha))
+    return out
+
+
+def grayscale_alpha(image):
+    return grayscale(image, alpha=True)
+
+
 def convert_pixels(image, dst_channels: int, dst_dtype, *, mode: int = L.CAST, coefs=None):
     """Pixel-format conversion of a (h, w, c) / (n, c) array: mode CAST = DynamicImage::to_*,
     mode CONVERT = ImageBuffer::convert."""

@@ -184,3 +184,25 @@ class DynamicImage:
         """DynamicImage::thumbnail (src/images/dynimage.rs:1159): aspect ratio kept, no fill."""
         w2, h2 = imageops.resize_dimensions(self.width, self.height, nwidth, nheight, False)
         return self.thumbnail_exact(w2, h2)
+
+    # ---- colorops (src/images/dynimage.rs:1082-1118, 1302-1339) ----
+    def grayscale(self) -> "DynamicImage":
+        """Luma stays Luma (clone); LumaA / Rgba keep their alpha (grayscale_alpha); Rgb -> Luma."""
+        c = self.buf.channels
+        if c == 1:
+            d = self.buf.data
+            return DynamicImage(ImageBuffer(d.clone() if imageops._is_torch(d) else d.copy()), self.luma_coefs)
+        return DynamicImage(ImageBuffer(imageops.grayscale(self.buf.data, alpha=c in (2, 4))), self.luma_coefs)
+
+    def invert(self) -> None:
+        """In place, like DynamicImage::invert(&mut self)."""
+        imageops.invert(self.buf.data)
+
+    def adjust_contrast(self, c: float) -> "DynamicImage":
+        return DynamicImage(ImageBuffer(imageops.contrast(self.buf.data, c)), self.luma_coefs)
+
+    def brighten(self, value: int) -> "DynamicImage":
+        return DynamicImage(ImageBuffer(imageops.brighten(self.buf.data, value)), self.luma_coefs)
+
+    def huerotate(self, value: int) -> "DynamicImage":
+        return DynamicImage(ImageBuffer(imageops.huerotate(self.buf.data, value)), self.luma_coefs)

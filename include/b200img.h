@@ -248,6 +248,31 @@ int b200img_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int
 int b200img_unsharpen_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
                           float sigma, int threshold, int flags, void *stream);
 
+/* ---- elementwise colour operators (src/imageops/colorops.rs) ---------------
+ * All bit-exact.  `dst` may be `src`: that is the reference's *_in_place form.
+ *   invert      colorops.rs:70-83 (Invert impls, src/color.rs:973-1015): max - c, alpha kept
+ *   brighten    colorops.rs:161-186 (brighten_in_place 194-221): clamp(c + value, 0, max) in i32 on
+ *               the colour channels; f32 subpixels go through the reference's i32 cast too
+ *   contrast    colorops.rs:92-118 (contrast_in_place 126-152): f32, every channel, truncating cast
+ *   huerotate   colorops.rs:232-290 (huerotate_in_place 295-349): f64 matrix on the first three
+ *               channels, clamp to [0, 255] whatever the subpixel type; < 3 channels: copy
+ *   grayscale / grayscale_alpha  colorops.rs:14-66: pixel.to_luma() in the source subpixel type
+ *               (dst has 1 channel, or 2 with keep_alpha) */
+int b200img_invert(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst);
+int b200img_invert_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst, void *stream);
+int b200img_brighten(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst, int32_t value);
+int b200img_brighten_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                         int32_t value, void *stream);
+int b200img_contrast(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst, float contrast);
+int b200img_contrast_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                         float contrast, void *stream);
+int b200img_huerotate(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst, int32_t degrees);
+int b200img_huerotate_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                          int32_t degrees, void *stream);
+int b200img_grayscale(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst, int keep_alpha);
+int b200img_grayscale_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
+                          int keep_alpha, void *stream);
+
 /* ---- pixel-format conversions --------------------------------------------
  * mode CAST    = DynamicImage::to_* / into_* (src/images/dynimage.rs:320-568
  *                -> CicpRgb::cast_pixels src/metadata/cicp.rs:706-1033;

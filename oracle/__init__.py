@@ -79,6 +79,8 @@ def lib():
         L.orc_filter3x3.argtypes = [vp, u32, u32, i, i, vp, vp]
         L.orc_unsharpen.argtypes = [vp, u32, u32, i, i, vp, f, C.c_int32]
         L.orc_thumbnail.argtypes = [vp, u32, u32, i, i, vp, u32, u32]
+        L.orc_colorop.argtypes = [i, vp, vp, sz, i, i, C.c_int32, f]
+        L.orc_huerotate_matrix.argtypes = [C.c_int32, vp]; L.orc_huerotate_matrix.restype = None
         pu32 = C.POINTER(u32)
         L.orc_resize_dimensions.argtypes = [u32, u32, u32, u32, i, pu32, pu32]
         L.orc_resize_dimensions.restype = None
@@ -279,3 +281,46 @@ def thumbnail(img, nw: int, nh: int):
     if rc:
         raise RuntimeError(f"orc_thumbnail rc={rc}")
     return out
+
+
+def _colorop(op, img, ivalue=0, fvalue=0.0):
+    a = _img(img)
+    h, w, c = a.shape
+    out = np.zeros_like(a)
+    rc = lib().orc_colorop(op, _ptr(a), _ptr(out), h * w, c, _DT[a.dtype], int(ivalue), float(fvalue))
+    if rc:
+        raise RuntimeError(f"orc_colorop rc={rc}")
+    return out
+
+
+def invert(img):
+    """imageops::invert (src/imageops/colorops.rs:70)."""
+    return _colorop(0, img)
+
+
+def brighten(img, value: int):
+    """imageops::brighten (colorops.rs:161)."""
+    return _colorop(1, img, ivalue=value)
+
+
+def contrast(img, contrast: float):
+    """imageops::contrast (colorops.rs:92)."""
+    return _colorop(2, img, fvalue=contrast)
+
+
+def huerotate(img, degrees: int):
+    """imageops::huerotate (colorops.rs:232)."""
+    return _colorop(3, img, ivalue=degrees)
+
+
+def huerotate_matrix(degrees: int):
+    m = np.zeros(9, np.float64)
+    lib().orc_huerotate_matrix(int(degrees), _ptr(m))
+    return m
+
+
+def grayscale(img, alpha: bool = False):
+    """imageops::grayscale / grayscale_alpha (colorops.rs:14-66): pixel.to_luma() in the source type."""
+    a = _img(img)
+    h, w, c = a.shape
+    return convert(a.reshape(-1, c), c, a.dtype, 2 if alpha else 1, CONVERT).reshape(h, w, 2 if alpha else 1)

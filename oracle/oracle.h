@@ -98,6 +98,12 @@ int orc_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int dty
 int orc_thumbnail(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
                   uint32_t nw, uint32_t nh);
 
+/* colorops.rs: op 0 invert (70-83), 1 brighten(ivalue) (161-186), 2 contrast(fvalue) (92-118),
+ * 3 huerotate(ivalue degrees) (232-290).  dst may alias src (the *_in_place forms). */
+int orc_colorop(int op, const void *src, void *dst, size_t npixels, int channels, int dtype,
+                int32_t ivalue, float fvalue);
+void orc_huerotate_matrix(int32_t value, double m[9]);
+
 /* ---- host helper (src/math/utils.rs:56-84) ------------------------------ */
 void orc_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill,
                            uint32_t *ow, uint32_t *oh);

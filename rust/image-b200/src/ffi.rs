@@ -97,6 +97,17 @@ extern "C" {
     pub fn b200img_unsharpen_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                                  sigma: c_float, threshold: c_int, flags: c_int, stream: Stream) -> c_int;
 
+    pub fn b200img_invert(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void) -> c_int;
+    pub fn b200img_invert_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, stream: Stream) -> c_int;
+    pub fn b200img_brighten(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, value: i32) -> c_int;
+    pub fn b200img_brighten_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, value: i32, stream: Stream) -> c_int;
+    pub fn b200img_contrast(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, contrast: c_float) -> c_int;
+    pub fn b200img_contrast_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, contrast: c_float, stream: Stream) -> c_int;
+    pub fn b200img_huerotate(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, degrees: i32) -> c_int;
+    pub fn b200img_huerotate_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, degrees: i32, stream: Stream) -> c_int;
+    pub fn b200img_grayscale(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, keep_alpha: c_int) -> c_int;
+    pub fn b200img_grayscale_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, keep_alpha: c_int, stream: Stream) -> c_int;
+
     pub fn b200img_convert(src: *const c_void, src_dtype: c_int, src_channels: c_int, dst: *mut c_void, dst_dtype: c_int,
                            dst_channels: c_int, npixels: usize, mode: c_int, coefs: *const c_float) -> c_int;
     pub fn b200img_convert_dev(src: *const c_void, src_dtype: c_int, src_channels: c_int, dst: *mut c_void,

@@ -303,3 +303,28 @@ def test_thumbnail_oracle_invariants():
     assert not o.thumbnail(np.zeros((0, 4, 1), np.uint8), 3, 3).any()
     with pytest.raises(o.ReferencePanic):                         # integer division by a zero count
         o.thumbnail(np.zeros((1000, 100, 1), np.uint8), 1, 1)
+
+
+# ---- colorops restatements, pinned by colorops.rs:657-700 --------------------------------
+def test_colorops_reference_kats():
+    img = np.array([0, 1, 2, 10, 11, 12], np.uint8).reshape(2, 3, 1)
+    assert o.grayscale(img).ravel().tolist() == [0, 1, 2, 10, 11, 12]                 # test_grayscale
+    assert o.invert(img).ravel().tolist() == [255, 254, 253, 245, 244, 243]           # test_invert
+    assert o.brighten(img, 10).ravel().tolist() == [10, 11, 12, 20, 21, 22]           # test_brighten(_place)
+
+
+def test_colorops_oracle_invariants():
+    rng = np.random.default_rng(8)
+    rgba = rng.integers(0, 256, (5, 6, 4), dtype=np.uint8)
+    assert np.array_equal(o.invert(rgba)[..., 3], rgba[..., 3])                       # alpha kept
+    assert np.array_equal(o.invert(o.invert(rgba)), rgba)
+    assert np.array_equal(o.brighten(rgba, 300)[..., :3], np.full((5, 6, 3), 255))
+    assert np.array_equal(o.huerotate(rgba, 0), rgba)
+    la = rng.integers(0, 65536, (4, 4, 2), dtype=np.uint16)
+    assert np.array_equal(o.huerotate(la, 90), la)                                    # < 3 channels: copy
+    rgb16 = rng.integers(0, 65536, (4, 4, 3), dtype=np.uint16)
+    assert o.huerotate(rgb16, 30).max() <= 255                                        # the literal clamp to 255
+    f = np.array([[[0.2, 0.7, 1.0, 0.5]]], np.float32)
+    assert o.brighten(f, 1).ravel().tolist() == [1.0, 1.0, 1.0, 0.5]                  # f32 goes through the i32 cast
+    m = o.huerotate_matrix(0)
+    assert np.allclose(m.reshape(3, 3), np.eye(3), atol=1e-12)

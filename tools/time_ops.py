@@ -48,6 +48,16 @@ for tdt, dt, name in ((torch.uint8, L.U8, "u8"), (torch.uint16, L.U16, "u16"), (
         dst = torch.empty((n, 2160, 3840, 3), dtype=tdt, device=dev)
         fn = lambda: L.check(lib.b200img_thumbnail_batch_dev(small.data_ptr(), 960, 540, 3, dt, dst.data_ptr(), 3840, 2160, n, 0, st))
         timed(fn, small.numel() * es + dst.numel() * es, f"thumbnail {name} 8x(960x540) -> 4K (upscale)")
+    tall = src.view(n * h, w, 3)   # the elementwise operators see the batch as one tall image
+    nb = 2 * tall.numel() * es
+    timed(lambda: imageops.invert(tall), nb, f"invert {name} 8x4K (in place)")
+    timed(lambda: imageops.brighten_in_place(tall, 10), nb, f"brighten {name} 8x4K (in place)")
+    timed(lambda: imageops.contrast_in_place(tall, 15.0), nb, f"contrast {name} 8x4K (in place)")
+    timed(lambda: imageops.huerotate_in_place(tall, 45), nb, f"huerotate {name} 8x4K (in place)")
+    gray = torch.empty((n * h, w, 1), dtype=tdt, device=dev)
+    timed(lambda: L.check(lib.b200img_grayscale_dev(tall.data_ptr(), w, n * h, 3, dt, gray.data_ptr(), 0, st)),
+          tall.numel() * es + gray.numel() * es, f"grayscale {name} 8x4K")
+    del gray
     one = src[0]
     timed(lambda: imageops.filter3x3(one, [1, 1, 1, 1, -8, 1, 1, 1, 1]), 2 * one.numel() * es, f"filter3x3 {name} 4K")
     timed(lambda: imageops.unsharpen(one, 2.0, 0), 2 * one.numel() * es, f"unsharpen {name} 4K sigma=2")
