@@ -81,6 +81,13 @@ SIGNATURES = {
     "b200img_filter3x3_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp, _vp]),
     "b200img_unsharpen": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i]),
     "b200img_unsharpen_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _i, _i, _vp]),
+    "b200img_has_constant_alpha": (_i, [_vp, _u32, _u32, _i, _i, C.POINTER(C.c_int)]),
+    "b200img_has_constant_alpha_dev": (_i, [_vp, _u32, _u32, _i, _i, C.POINTER(C.c_int), _vp]),
+    "b200img_premultiply_alpha": (_i, [_vp, _u32, _u32, _i, _i]),
+    "b200img_premultiply_alpha_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp]),
+    "b200img_unpremultiply_alpha": (_i, [_vp, _u32, _u32, _i, _i]),
+    "b200img_unpremultiply_alpha_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp]),
+    "b200img_convert_resize": (_i, [_vp, _i, _i, _u32, _u32, _vp, _i, _i, _u32, _u32, _i, _f, _i]),
     "b200img_invert": (_i, [_vp, _u32, _u32, _i, _i, _vp]),
     "b200img_invert_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _vp]),
     "b200img_brighten": (_i, [_vp, _u32, _u32, _i, _i, _vp, C.c_int32]),

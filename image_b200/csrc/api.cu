@@ -33,6 +33,8 @@ int thumbnail_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
                      uint32_t n_images, int path, cudaStream_t st);
 int colorop_launch(int op, const void *src, void *dst, size_t npixels, int C, int dtype, int32_t ivalue, float fvalue,
                    cudaStream_t st);
+int alpha_scan_launch(const void *src, size_t npixels, int C, int dtype, int *d_flag, cudaStream_t st);
+int alpha_mul_launch(void *buf, size_t npixels, int C, int dtype, bool un, cudaStream_t st);
 int filter3x3_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      const float kernel[9], cudaStream_t st);
 int unsharpen_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images, float sigma,
@@ -669,6 +671,101 @@ int b200img_grayscale_dev(const void *src, uint32_t w, uint32_t h, int C, int dt
     int rc = check_image("grayscale", C, dtype, w, h, &bytes);
     if (rc) return rc;
     return b200img_convert_dev(src, dtype, C, dst, dtype, keep_alpha ? 2 : 1, (size_t)w * h, B200IMG_CONVERT, nullptr, stream);
+}
+
+// ---- either side of DynamicImage::resize (src/imageops/resize.rs) ------------
+static int constant_alpha_on(const void *d_src, size_t npix, int C, int dtype, int *result, cudaStream_t st) {
+    void *flag;
+    int rc = scratch(SCRATCH_FLAG, sizeof(int), &flag);
+    if (rc) return rc;
+    if ((rc = alpha_scan_launch(d_src, npix, C, dtype, (int *)flag, st))) return rc;
+    int differs = 0;
+    B200_CUDA(cudaMemcpyAsync(&differs, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    B200_CUDA(cudaStreamSynchronize(st));
+    *result = differs ? 0 : 1;
+    return B200IMG_OK;
+}
+
+int b200img_has_constant_alpha_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, int *result, void *stream) {
+    size_t bytes;
+    int rc = check_image("has_constant_alpha", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (!result) return fail(B200IMG_ERR_BAD_ARG, "has_constant_alpha: null result");
+    *result = 1;
+    if (bytes == 0 || (C != 2 && C != 4)) return B200IMG_OK;  // resize.rs:155-171: no alpha channel / empty image
+    if (!src) return fail(B200IMG_ERR_BAD_ARG, "has_constant_alpha: null buffer");
+    set_scratch_stream((cudaStream_t)stream);
+    return constant_alpha_on(src, (size_t)w * h, C, dtype, result, (cudaStream_t)stream);
+}
+
+int b200img_has_constant_alpha(const void *src, uint32_t w, uint32_t h, int C, int dtype, int *result) {
+    size_t bytes;
+    int rc = check_image("has_constant_alpha", C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (!result) return fail(B200IMG_ERR_BAD_ARG, "has_constant_alpha: null result");
+    *result = 1;
+    if (bytes == 0 || (C != 2 && C != 4)) return B200IMG_OK;
+    if (!src) return fail(B200IMG_ERR_BAD_ARG, "has_constant_alpha: null buffer");
+    HostCall hc;
+    void *ds;
+    if ((rc = hc.in(src, bytes, &ds))) return rc;
+    return constant_alpha_on(ds, (size_t)w * h, C, dtype, result, 0);
+}
+
+static int alpha_mul_dev(const char *name, void *buf, uint32_t w, uint32_t h, int C, int dtype, bool un, void *stream) {
+    size_t bytes;
+    int rc = check_image(name, C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0 || (C != 2 && C != 4)) return B200IMG_OK;
+    if (!buf) return fail(B200IMG_ERR_BAD_ARG, "%s: null buffer", name);
+    return alpha_mul_launch(buf, (size_t)w * h, C, dtype, un, (cudaStream_t)stream);
+}
+
+static int alpha_mul_host(const char *name, void *buf, uint32_t w, uint32_t h, int C, int dtype, bool un) {
+    size_t bytes;
+    int rc = check_image(name, C, dtype, w, h, &bytes);
+    if (rc) return rc;
+    if (bytes == 0 || (C != 2 && C != 4)) return B200IMG_OK;
+    if (!buf) return fail(B200IMG_ERR_BAD_ARG, "%s: null buffer", name);
+    HostCall hc;
+    void *d;
+    if ((rc = hc.in(buf, bytes, &d))) return rc;
+    if ((rc = alpha_mul_launch(d, (size_t)w * h, C, dtype, un, 0))) return rc;
+    return hc.out(buf, d, bytes);
+}
+
+int b200img_premultiply_alpha(void *buf, uint32_t w, uint32_t h, int C, int dtype) {
+    return alpha_mul_host("premultiply_alpha", buf, w, h, C, dtype, false);
+}
+int b200img_premultiply_alpha_dev(void *buf, uint32_t w, uint32_t h, int C, int dtype, void *stream) {
+    return alpha_mul_dev("premultiply_alpha", buf, w, h, C, dtype, false, stream);
+}
+int b200img_unpremultiply_alpha(void *buf, uint32_t w, uint32_t h, int C, int dtype) {
+    return alpha_mul_host("unpremultiply_alpha", buf, w, h, C, dtype, true);
+}
+int b200img_unpremultiply_alpha_dev(void *buf, uint32_t w, uint32_t h, int C, int dtype, void *stream) {
+    return alpha_mul_dev("unpremultiply_alpha", buf, w, h, C, dtype, true, stream);
+}
+
+// decode -> device hand-off: one upload, DynamicImage::to_* on the device, imageops::resize, one download
+int b200img_convert_resize(const void *src, int src_dtype, int src_channels, uint32_t w, uint32_t h, void *dst, int dst_dtype,
+                           int dst_channels, uint32_t nw, uint32_t nh, int filter, float acc_init, int flags) {
+    size_t sb, mb, db;
+    int rc = check_image("convert_resize", src_channels, src_dtype, w, h, &sb);
+    if (rc) return rc;
+    if ((rc = check_image("convert_resize", dst_channels, dst_dtype, w, h, &mb))) return rc;
+    if ((rc = check_image("convert_resize", dst_channels, dst_dtype, nw, nh, &db))) return rc;
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "convert_resize: unknown filter %d", filter);
+    if (db == 0) return B200IMG_OK;
+    if (!dst || (sb && !src)) return fail(B200IMG_ERR_BAD_ARG, "convert_resize: null buffer");
+    HostCall hc;
+    void *ds, *dm, *dd;
+    if ((rc = hc.in(src, sb, &ds))) return rc;
+    if ((rc = scratch(SCRATCH_MID, mb ? mb : 1, &dm))) return rc;
+    if ((rc = hc.out_buf(db, &dd))) return rc;
+    if (sb && (rc = convert_dev(ds, src_dtype, src_channels, dm, dst_dtype, dst_channels, (size_t)w * h, 0, nullptr, 0, 0))) return rc;
+    if ((rc = resize_front(dm, 0, w, h, dst_channels, dst_dtype, dd, 0, nw, nh, 1, filter, acc_init, flags, 0))) return rc;
+    return hc.out(dst, dd, db);
 }
 
 // ---- conversions and swizzle ----------------------------------------------------

@@ -31,7 +31,7 @@ DeviceCtx *current_ctx();
 
 // Cached scratch allocation on the current device, at least `bytes` large.
 // Slots are independent buffers; contents are undefined on return.
-enum ScratchSlot { SCRATCH_TABLES = 0, SCRATCH_A = 1, SCRATCH_B = 2, SCRATCH_IO_SRC = 3, SCRATCH_IO_DST = 4, SCRATCH_SLOTS = 5 };
+enum ScratchSlot { SCRATCH_TABLES = 0, SCRATCH_A = 1, SCRATCH_B = 2, SCRATCH_IO_SRC = 3, SCRATCH_IO_DST = 4, SCRATCH_MID = 5, SCRATCH_FLAG = 6, SCRATCH_SLOTS = 7 };
 int scratch(ScratchSlot slot, size_t bytes, void **out);
 // Scratch is keyed by (device, stream): entry points name their stream before asking for scratch.
 void set_scratch_stream(cudaStream_t st);

@@ -294,6 +294,53 @@ def unsharpen(image, sigma: float, threshold: int, *, flags: int = L.FP_FAST):
     return out
 
 
+def has_constant_alpha(image) -> bool:
+    """has_constant_alpha (src/imageops/resize.rs:155-218)."""
+    im = _Img(image)
+    res = C.c_int(1)
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(lib.b200img_has_constant_alpha_dev, im.ptr, im.w, im.h, im.c, im.dt, C.byref(res), _stream(im.a))
+    else:
+        _call(lib.b200img_has_constant_alpha, im.ptr, im.w, im.h, im.c, im.dt, C.byref(res))
+    return bool(res.value)
+
+
+def _alpha_mul(name: str, image):
+    im = _Img(image)
+    lib = L.lib()
+    if im.torch:
+        with _on_device(im):
+            _call(getattr(lib, f"b200img_{name}_dev"), im.ptr, im.w, im.h, im.c, im.dt, _stream(im.a))
+    else:
+        _call(getattr(lib, f"b200img_{name}"), im.ptr, im.w, im.h, im.c, im.dt)
+    return image
+
+
+def premultiply_alpha(image):
+    """In place.  The reference calls pic-scale-safe here (resize.rs:105-129): parity unpinned."""
+    return _alpha_mul("premultiply_alpha", image)
+
+
+def unpremultiply_alpha(image):
+    """In place (resize.rs:132-151); parity unpinned."""
+    return _alpha_mul("unpremultiply_alpha", image)
+
+
+def convert_resize(image, dst_channels: int, dst_dtype, nwidth: int, nheight: int, filter: FilterType, *,
+                   acc_init: float = ACC_INIT_REFERENCE, flags: int = L.FP_FAST):
+    """Decode hand-off for a HOST image: upload once, DynamicImage::to_* on the device, resize, download."""
+    a = np.ascontiguousarray(image)
+    if a.ndim == 2:
+        a = a[:, :, None]
+    h, w, c = a.shape
+    out = np.empty((nheight, nwidth, dst_channels), np.dtype(dst_dtype))
+    _call(L.lib().b200img_convert_resize, a.ctypes.data, _NP2DT[a.dtype], c, w, h, out.ctypes.data, _NP2DT[out.dtype],
+          dst_channels, nwidth, nheight, int(filter), float(acc_init), flags)
+    return out
+
+
 def _colorop(name: str, image, *params, out=None):
     im = _Img(image)
     if out is None:

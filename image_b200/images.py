@@ -135,8 +135,22 @@ class DynamicImage:
     # The reference routes DynamicImage::resize* to the third-party pic-scale-safe crate
     # (src/imageops/resize.rs); per the project's north star the drop-in runs the in-tree
     # sample.rs arithmetic instead ("resize boundary").
-    def resize_exact(self, nwidth, nheight, filter: FilterType, **kw) -> "DynamicImage":
-        return DynamicImage(ImageBuffer(imageops.resize(self.buf.data, nwidth, nheight, filter, **kw)), self.luma_coefs)
+    # The control flow around it is the reference's (resize.rs:13-93): same size -> unchanged; any
+    # filter but Nearest on an image whose alpha is not constant -> premultiply, resample,
+    # unpremultiply (that arithmetic is pic-scale-safe's too: parity unpinned; `premultiply=False`
+    # resamples straight alpha).
+    def resize_exact(self, nwidth, nheight, filter: FilterType, *, premultiply: bool = True, **kw) -> "DynamicImage":
+        if (nwidth, nheight) == (self.width, self.height):
+            return self
+        d = self.buf.data
+        pre = premultiply and filter != FilterType.Nearest and not imageops.has_constant_alpha(d)
+        if pre:
+            d = d.clone() if imageops._is_torch(d) else d.copy()
+            imageops.premultiply_alpha(d)
+        out = imageops.resize(d, nwidth, nheight, filter, **kw)
+        if pre:
+            imageops.unpremultiply_alpha(out)
+        return DynamicImage(ImageBuffer(out), self.luma_coefs)
 
     def resize(self, nwidth, nheight, filter: FilterType, **kw) -> "DynamicImage":
         if (nwidth, nheight) == (self.width, self.height):

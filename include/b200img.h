@@ -248,6 +248,26 @@ int b200img_unsharpen(const void *src, uint32_t w, uint32_t h, int channels, int
 int b200img_unsharpen_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype, void *d_dst,
                           float sigma, int threshold, int flags, void *stream);
 
+/* ---- either side of DynamicImage::resize (src/imageops/resize.rs) -----------
+ * has_constant_alpha: resize.rs:155-218, restated exactly (integer alphas XOR-ed with the first
+ * pixel's and summed; f32 alphas compared with ==, so a NaN alpha is never constant; no alpha
+ * channel or an empty image = constant).  *result = 1 / 0.  The _dev form synchronises `stream`.
+ * premultiply / unpremultiply (in place; LumaA and Rgba only, others untouched): the reference
+ * calls the unvendored pic-scale-safe crate here -- PARITY UNPINNED; this library rounds to
+ * nearest: (c*a + max/2)/max, and min((c*max + a/2)/a, max) with a = 0 keeping c; f32: c*a, c/a.
+ * convert_resize: the decode hand-off -- one upload of the decoded buffer, DynamicImage::to_*
+ * (B200IMG_CAST) on the device, imageops::resize, one download. */
+int b200img_has_constant_alpha(const void *src, uint32_t w, uint32_t h, int channels, int dtype, int *result);
+int b200img_has_constant_alpha_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
+                                   int *result, void *stream);
+int b200img_premultiply_alpha(void *buf, uint32_t w, uint32_t h, int channels, int dtype);
+int b200img_premultiply_alpha_dev(void *d_buf, uint32_t w, uint32_t h, int channels, int dtype, void *stream);
+int b200img_unpremultiply_alpha(void *buf, uint32_t w, uint32_t h, int channels, int dtype);
+int b200img_unpremultiply_alpha_dev(void *d_buf, uint32_t w, uint32_t h, int channels, int dtype, void *stream);
+int b200img_convert_resize(const void *src, int src_dtype, int src_channels, uint32_t w, uint32_t h,
+                           void *dst, int dst_dtype, int dst_channels, uint32_t nw, uint32_t nh,
+                           int filter, float acc_init, int flags);
+
 /* ---- elementwise colour operators (src/imageops/colorops.rs) ---------------
  * All bit-exact.  `dst` may be `src`: that is the reference's *_in_place form.
  *   invert      colorops.rs:70-83 (Invert impls, src/color.rs:973-1015): max - c, alpha kept

@@ -79,6 +79,8 @@ def lib():
         L.orc_filter3x3.argtypes = [vp, u32, u32, i, i, vp, vp]
         L.orc_unsharpen.argtypes = [vp, u32, u32, i, i, vp, f, C.c_int32]
         L.orc_thumbnail.argtypes = [vp, u32, u32, i, i, vp, u32, u32]
+        L.orc_has_constant_alpha.argtypes = [vp, u32, u32, i, i]
+        L.orc_alpha_mul.argtypes = [vp, sz, i, i, i]
         L.orc_colorop.argtypes = [i, vp, vp, sz, i, i, C.c_int32, f]
         L.orc_huerotate_matrix.argtypes = [C.c_int32, vp]; L.orc_huerotate_matrix.restype = None
         pu32 = C.POINTER(u32)
@@ -324,3 +326,18 @@ def grayscale(img, alpha: bool = False):
     a = _img(img)
     h, w, c = a.shape
     return convert(a.reshape(-1, c), c, a.dtype, 2 if alpha else 1, CONVERT).reshape(h, w, 2 if alpha else 1)
+
+
+def has_constant_alpha(img) -> bool:
+    """has_constant_alpha (src/imageops/resize.rs:155-218)."""
+    a = _img(img)
+    h, w, c = a.shape
+    return bool(lib().orc_has_constant_alpha(_ptr(a), w, h, c, _DT[a.dtype]))
+
+
+def alpha_mul(img, un: bool):
+    """The product's own premultiply / unpremultiply rule (the reference's is pic-scale-safe's: unpinned)."""
+    a = _img(img).copy()
+    h, w, c = a.shape
+    lib().orc_alpha_mul(_ptr(a), h * w, c, _DT[a.dtype], int(un))
+    return a

@@ -8,6 +8,7 @@
 #include "oracle.h"
 #include "rust_sem.h"
 
+#include <algorithm>
 #include <cmath>
 
 namespace {
@@ -119,4 +120,70 @@ extern "C" int orc_colorop(int op, const void *src, void *dst, size_t npixels, i
     }
 #undef DISPATCH
     return -1;
+}
+
+/* ---- either side of DynamicImage::resize (src/imageops/resize.rs) -------------------------- */
+namespace {
+// has_constant_alpha_integer, resize.rs:173-202: XOR with the first alpha, summed per row
+template <typename T>
+int constant_alpha_int(const T *src, uint32_t w, uint32_t h, int C) {
+    if ((size_t)w * h == 0) return 1;
+    const T first = src[C - 1];
+    uint64_t sum_of_diffs = 0;
+    for (uint32_t y = 0; y < h; ++y) {
+        const T *row = src + (size_t)y * w * C;
+        for (uint32_t x = 0; x < w; ++x) sum_of_diffs += (uint64_t)(T)(row[x * C + C - 1] ^ first);
+        if (sum_of_diffs != 0) return 0;
+    }
+    return 1;
+}
+// has_constant_alpha_f32, resize.rs:205-218
+int constant_alpha_f32(const float *src, uint32_t w, uint32_t h, int C) {
+    const size_t n = (size_t)w * h;
+    if (n == 0) return 1;
+    const float first = src[C - 1];
+    for (size_t i = 0; i < n; ++i)
+        if (!(src[i * C + C - 1] == first)) return 0;
+    return 1;
+}
+// The premultiply arithmetic of the reference lives in pic-scale-safe (unvendored): this is the
+// product's documented own rule, restated -- a consistency check, not reference parity.
+template <typename T>
+void alpha_mul_int(T *buf, size_t npix, int C, uint32_t mx, int un) {
+    for (size_t i = 0; i < npix; ++i) {
+        const uint32_t a = buf[i * C + C - 1];
+        for (int c = 0; c < C - 1; ++c) {
+            const uint32_t v = buf[i * C + c];
+            if (!un) buf[i * C + c] = (T)((v * a + mx / 2) / mx);
+            else if (a != 0) buf[i * C + c] = (T)std::min<uint32_t>((v * mx + a / 2) / a, mx);
+        }
+    }
+}
+}  // namespace
+
+extern "C" int orc_has_constant_alpha(const void *src, uint32_t w, uint32_t h, int channels, int dtype) {
+    if (channels != 2 && channels != 4) return 1;  /* resize.rs:155-171: Luma / Rgb variants */
+    switch (dtype) {
+        case ORC_U8: return constant_alpha_int((const uint8_t *)src, w, h, channels);
+        case ORC_U16: return constant_alpha_int((const uint16_t *)src, w, h, channels);
+        case ORC_F32: return constant_alpha_f32((const float *)src, w, h, channels);
+    }
+    return -1;
+}
+
+extern "C" int orc_alpha_mul(void *buf, size_t npixels, int channels, int dtype, int un) {
+    if (channels != 2 && channels != 4) return 0;
+    if (dtype == ORC_U8) alpha_mul_int((uint8_t *)buf, npixels, channels, 255u, un);
+    else if (dtype == ORC_U16) alpha_mul_int((uint16_t *)buf, npixels, channels, 65535u, un);
+    else {
+        float *f = (float *)buf;
+        for (size_t i = 0; i < npixels; ++i) {
+            const float a = f[i * channels + channels - 1];
+            for (int c = 0; c < channels - 1; ++c) {
+                if (!un) f[i * channels + c] = f[i * channels + c] * a;
+                else if (a != 0.0f) f[i * channels + c] = f[i * channels + c] / a;
+            }
+        }
+    }
+    return 0;
 }

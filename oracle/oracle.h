@@ -104,6 +104,12 @@ int orc_colorop(int op, const void *src, void *dst, size_t npixels, int channels
                 int32_t ivalue, float fvalue);
 void orc_huerotate_matrix(int32_t value, double m[9]);
 
+/* has_constant_alpha (src/imageops/resize.rs:155-218): 1 / 0 */
+int orc_has_constant_alpha(const void *src, uint32_t w, uint32_t h, int channels, int dtype);
+/* NOT reference arithmetic (pic-scale-safe is unvendored): the product's own documented
+ * premultiply (un = 0) / unpremultiply (un = 1) rule, for a consistency check only */
+int orc_alpha_mul(void *buf, size_t npixels, int channels, int dtype, int un);
+
 /* ---- host helper (src/math/utils.rs:56-84) ------------------------------ */
 void orc_resize_dimensions(uint32_t w, uint32_t h, uint32_t nw, uint32_t nh, int fill,
                            uint32_t *ow, uint32_t *oh);

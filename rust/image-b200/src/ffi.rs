@@ -97,6 +97,15 @@ extern "C" {
     pub fn b200img_unsharpen_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                                  sigma: c_float, threshold: c_int, flags: c_int, stream: Stream) -> c_int;
 
+    pub fn b200img_has_constant_alpha(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, result: *mut c_int) -> c_int;
+    pub fn b200img_has_constant_alpha_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, result: *mut c_int, stream: Stream) -> c_int;
+    pub fn b200img_premultiply_alpha(buf: *mut c_void, w: u32, h: u32, channels: c_int, dtype: c_int) -> c_int;
+    pub fn b200img_premultiply_alpha_dev(buf: *mut c_void, w: u32, h: u32, channels: c_int, dtype: c_int, stream: Stream) -> c_int;
+    pub fn b200img_unpremultiply_alpha(buf: *mut c_void, w: u32, h: u32, channels: c_int, dtype: c_int) -> c_int;
+    pub fn b200img_unpremultiply_alpha_dev(buf: *mut c_void, w: u32, h: u32, channels: c_int, dtype: c_int, stream: Stream) -> c_int;
+    pub fn b200img_convert_resize(src: *const c_void, src_dtype: c_int, src_channels: c_int, w: u32, h: u32,
+                                  dst: *mut c_void, dst_dtype: c_int, dst_channels: c_int, nw: u32, nh: u32,
+                                  filter: c_int, acc_init: c_float, flags: c_int) -> c_int;
     pub fn b200img_invert(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void) -> c_int;
     pub fn b200img_invert_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, stream: Stream) -> c_int;
     pub fn b200img_brighten(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void, value: i32) -> c_int;

@@ -328,3 +328,16 @@ def test_colorops_oracle_invariants():
     assert o.brighten(f, 1).ravel().tolist() == [1.0, 1.0, 1.0, 0.5]                  # f32 goes through the i32 cast
     m = o.huerotate_matrix(0)
     assert np.allclose(m.reshape(3, 3), np.eye(3), atol=1e-12)
+
+
+def test_has_constant_alpha_oracle():
+    """resize.rs:155-218"""
+    rgba = np.zeros((6, 7, 4), np.uint8)
+    rgba[..., 3] = 200
+    assert o.has_constant_alpha(rgba)
+    rgba[5, 6, 3] = 201
+    assert not o.has_constant_alpha(rgba)
+    assert o.has_constant_alpha(np.arange(60, dtype=np.uint16).reshape(4, 5, 3))      # no alpha channel
+    assert o.has_constant_alpha(np.zeros((0, 3, 2), np.float32))                      # empty
+    nan = np.full((2, 2, 2), np.nan, np.float32)
+    assert not o.has_constant_alpha(nan)

@@ -32,6 +32,14 @@ def timed(fn, nbytes, label):
 
 
 n, w, h = 8, 3840, 2160
+# ---- either side of DynamicImage::resize: Rgba8 ----
+rgba = torch.randint(0, 256, (n * h, w, 4), device=dev, generator=g).to(torch.uint8)
+timed(lambda: imageops.has_constant_alpha(rgba), rgba.numel(), "has_constant_alpha u8 8x4K Rgba (varying; incl. sync + 4-byte D2H)")
+rgba[..., 3] = 255
+timed(lambda: imageops.has_constant_alpha(rgba), rgba.numel(), "has_constant_alpha u8 8x4K Rgba (constant)")
+timed(lambda: imageops.premultiply_alpha(rgba), 2 * rgba.numel(), "premultiply_alpha u8 8x4K Rgba (in place)")
+timed(lambda: imageops.unpremultiply_alpha(rgba), 2 * rgba.numel(), "unpremultiply_alpha u8 8x4K Rgba (in place)")
+del rgba
 for tdt, dt, name in ((torch.uint8, L.U8, "u8"), (torch.uint16, L.U16, "u16"), (torch.float32, L.F32, "f32")):
     if tdt == torch.float32:
         src = torch.rand((n, h, w, 3), device=dev, generator=g)
