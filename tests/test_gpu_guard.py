@@ -1,0 +1,70 @@
+"""Out-of-bounds WRITE check for every device entry point: the destination sits between two guard
+bands inside a larger allocation; the bands must come back untouched and the result must equal
+the one computed into a plain buffer.  (compute-sanitizer is not available on the GPU pool.)"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import rand_image
+from image_b200 import FilterType, GaussianBlurParameters
+from image_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+GUARD = 512          # bytes; keeps 16-byte alignment of the destination
+DT = {np.dtype(np.uint8): L.U8, np.dtype(np.uint16): L.U16, np.dtype(np.float32): L.F32}
+
+
+def guarded(cuda, nbytes, call, offset=0):
+    """call(dst_ptr) twice: into a guarded buffer (optionally shifted by `offset` bytes) and a plain one"""
+    import torch
+    buf = torch.full((GUARD + offset + nbytes + GUARD,), 0xA5, dtype=torch.uint8, device=cuda)
+    L.check(call(buf.data_ptr() + GUARD + offset))
+    plain = torch.zeros(max(nbytes, 1), dtype=torch.uint8, device=cuda)
+    L.check(call(plain.data_ptr()))
+    torch.cuda.synchronize()
+    b = buf.cpu().numpy()
+    lo, hi = GUARD + offset, GUARD + offset + nbytes
+    assert (b[:lo] == 0xA5).all(), "wrote before the destination"
+    assert (b[hi:] == 0xA5).all(), "wrote past the destination"
+    assert np.array_equal(b[lo:hi], plain.cpu().numpy()[:nbytes])
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_guard_bands(cuda, dtype, c):
+    import torch
+    lib = L.lib()
+    rng = np.random.default_rng(200 + c)
+    es = np.dtype(dtype).itemsize
+    dt = DT[np.dtype(dtype)]
+    st = torch.cuda.current_stream().cuda_stream
+    for (h, w) in ((37, 53), (64, 96)):
+        img = rand_image(rng, h, w, c, dtype)
+        src = torch.from_numpy(img).to(cuda)
+        sp = src.data_ptr()
+        n = h * w * c * es
+        offs = (0, es)  # aligned and element-shifted destinations
+        for off in offs:
+            for f in (FilterType.Nearest, FilterType.Triangle, FilterType.Lanczos3):
+                for (nw, nh) in ((21, 17), (71, 83), (w, 9)):
+                    guarded(cuda, nw * nh * c * es, lambda d: lib.b200img_resize_dev(sp, w, h, c, dt, d, nw, nh, int(f), 1.0, 0, st), off)
+            for (nw, nh) in ((13, 11), (90, 70), (w // 2, h // 2)):
+                guarded(cuda, nw * nh * c * es, lambda d: lib.b200img_thumbnail_dev(sp, w, h, c, dt, d, nw, nh, 0, st), off)
+            p = GaussianBlurParameters.new_from_sigma(2.0)
+            for path in (L.BLUR_GENERIC, L.BLUR_DYN):
+                guarded(cuda, n, lambda d: lib.b200img_gaussian_blur_dev(sp, w, h, c, dt, d, C.byref(p.raw), path, 0, st), off)
+            guarded(cuda, n, lambda d: lib.b200img_fast_blur_dev(sp, w, h, c, dt, d, 3.0, st), off)
+            k = (C.c_float * 9)(0, -1, 0, -1, 5, -1, 0, -1, 0)
+            guarded(cuda, n, lambda d: lib.b200img_filter3x3_dev(sp, w, h, c, dt, d, C.cast(k, C.c_void_p), st), off)
+            guarded(cuda, n, lambda d: lib.b200img_unsharpen_dev(sp, w, h, c, dt, d, 1.5, 2, 0, st), off)
+            guarded(cuda, n, lambda d: lib.b200img_invert_dev(sp, w, h, c, dt, d, st), off)
+            guarded(cuda, n, lambda d: lib.b200img_brighten_dev(sp, w, h, c, dt, d, 20, st), off)
+            guarded(cuda, n, lambda d: lib.b200img_contrast_dev(sp, w, h, c, dt, d, 10.0, st), off)
+            guarded(cuda, n, lambda d: lib.b200img_huerotate_dev(sp, w, h, c, dt, d, 30, st), off)
+            for keep in (0, 1):
+                guarded(cuda, h * w * (2 if keep else 1) * es, lambda d: lib.b200img_grayscale_dev(sp, w, h, c, dt, d, keep, st), off)
+            for dc, ddt, des in ((3, L.U8, 1), (4, L.F32, 4), (1, L.U16, 2)):
+                for mode in (L.CAST, L.CONVERT):
+                    guarded(cuda, h * w * dc * des, lambda d: lib.b200img_convert_dev(sp, dt, c, d, ddt, dc, h * w, mode, None, st),
+                            off if des <= es else 0)
