@@ -45,7 +45,8 @@ struct ResizeArgs {
     const int32_t *vleft, *vcount; const float *vw; int vstride;
     const int32_t *hleft, *hcount; const float *hw; int hstride;
     float acc_init;
-    int TW, TH;            // tile of the destination
+    int TW, TH;            // tile of the destination (powers of two)
+    int log2TW;
     int tiles_x, tiles_y;  // per image
     int max_cols, max_rows;     // bound of the staged source region (pixels, rows)
     int src_pitch;              // bytes per staged source row
@@ -65,7 +66,10 @@ resize_kernel(const ResizeArgs a) {
     float *s_tmp = reinterpret_cast<float *>(smem + src_bytes);
     float2 *s_vw = reinterpret_cast<float2 *>(s_tmp + (size_t)a.TH * a.tmp_pitch);  // [TH][vstride] (w, w)
     float2 *s_hw = s_vw + a.TH * a.vstride;                                          // [hstride][TW] (w, w)
-    int *s_hl = reinterpret_cast<int *>(s_hw + a.TW * a.hstride);
+    int *s_hl = reinterpret_cast<int *>(s_hw + a.TW * a.hstride);   // [TW] first float of a column's window in a tmp row
+    int *s_hn = s_hl + a.TW;                                        // [TW] taps of a column
+    int *s_vl = s_hn + a.TW;                                        // [TH] first staged row of a row's window
+    int *s_vn = s_vl + a.TH;                                        // [TH] taps of a row
     __shared__ __align__(8) uint64_t bar;
 
     const int tid = threadIdx.x;
@@ -137,7 +141,14 @@ resize_kernel(const ResizeArgs a) {
         const float w = a.hw[(size_t)(ox0 + oxl) * a.hstride + k];
         s_hw[k * a.TW + oxl] = make_float2(w, w);
     }
-    for (int i = tid; i < tw; i += THREADS) s_hl[i] = a.hleft[ox0 + i] * C - sub0;  // subpixel offset into a tmp row
+    for (int i = tid; i < tw; i += THREADS) {
+        s_hl[i] = a.hleft[ox0 + i] * C - sub0;  // subpixel offset into a tmp row
+        s_hn[i] = a.hcount[ox0 + i];
+    }
+    for (int i = tid; i < th; i += THREADS) {
+        s_vl[i] = a.vleft[oy0 + i] - row0;
+        s_vn[i] = a.vcount[oy0 + i];
+    }
 
     if (rows16) mbar_wait(&bar, 0);
     else cp_async_wait_all();
@@ -146,13 +157,15 @@ resize_kernel(const ResizeArgs a) {
     // ---- vertical pass: s_tmp[oyl][s] = acc_init + sum_i src[vleft+i][s] * vw[i] ----
     if (sizeof(T) == 4 && !STRICT && row_bytes % 16 == 0) {
         // f32 pixels: four subpixels per thread and tap (LDS.128 + 2 FFMA2)
+        // item = (row oyl, quad q), items walked THREADS apart without a division per item
         const int quads = row_bytes / 16;
         const f32x2 init2 = pack2(a.acc_init, a.acc_init);
-        for (int idx = tid; idx < th * quads; idx += THREADS) {
-            const int oyl = idx / quads, q = idx - oyl * quads;
-            const int l = a.vleft[oy0 + oyl] - row0, n = a.vcount[oy0 + oyl];
+        const int dy = THREADS / quads, dq = THREADS - dy * quads;
+        int oyl = tid / quads, q = tid - oyl * quads;
+        while (oyl < th) {
+            const int n = s_vn[oyl];
             const float2 *wv = s_vw + oyl * a.vstride;
-            const unsigned char *p = s_src + (size_t)l * a.src_pitch + q * 16;
+            const unsigned char *p = s_src + s_vl[oyl] * a.src_pitch + q * 16;
             f32x2 a01 = init2, a23 = init2;
             for (int i = 0; i < n; ++i) {
                 const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p);
@@ -161,18 +174,21 @@ resize_kernel(const ResizeArgs a) {
                 a23 = fma2(v.y, ww, a23);
                 p += a.src_pitch;
             }
-            *reinterpret_cast<ulonglong2 *>(s_tmp + (size_t)oyl * a.tmp_pitch + q * 4) = make_ulonglong2(a01, a23);
+            *reinterpret_cast<ulonglong2 *>(s_tmp + oyl * a.tmp_pitch + q * 4) = make_ulonglong2(a01, a23);
+            q += dq; oyl += dy;
+            if (q >= quads) { q -= quads; ++oyl; }
         }
     } else {
         constexpr int N = Word<T>::N;
         const int words = (row_sub + N - 1) / N;
         const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
-        for (int idx = tid; idx < th * words; idx += THREADS) {
-            const int oyl = idx / words, wd = idx - oyl * words;
-            const int l = a.vleft[oy0 + oyl] - row0, n = a.vcount[oy0 + oyl];
+        const int dy = THREADS / words, dw = THREADS - dy * words;
+        int oyl = tid / words, wd = tid - oyl * words;
+        while (oyl < th) {
+            const int n = s_vn[oyl];
             const float2 *wv = s_vw + oyl * a.vstride;
-            const unsigned char *p = s_src + (size_t)l * a.src_pitch + wd * 4;
-            float *t = s_tmp + (size_t)oyl * a.tmp_pitch + wd * N;
+            const unsigned char *p = s_src + s_vl[oyl] * a.src_pitch + wd * 4;
+            float *t = s_tmp + oyl * a.tmp_pitch + wd * N;
             if constexpr (!STRICT && N == 4) {
                 f32x2 a01 = pack2(a.acc_init, a.acc_init), a23 = a01;
                 for (int i = 0; i < n; ++i) {
@@ -209,6 +225,8 @@ resize_kernel(const ResizeArgs a) {
                 else if (N == 2) *reinterpret_cast<float2 *>(t) = make_float2(acc[0], acc[1 % N]);
                 else t[0] = acc[0];
             }
+            wd += dw; oyl += dy;
+            if (wd >= words) { wd -= words; ++oyl; }
         }
     }
     __syncthreads();
@@ -224,11 +242,11 @@ resize_kernel(const ResizeArgs a) {
     {
         const int items = a.TW * a.TH;  // lane = 8 rows x 4 columns: distinct banks for the float4 reads
         for (int e = tid; e < items; e += THREADS) {
-            const int oyl = (e / (8 * a.TW)) * 8 + (e & 7);
-            const int oxl = (e >> 3) % a.TW;
+            const int oyl = ((e >> (3 + a.log2TW)) << 3) | (e & 7);   // TW is a power of two
+            const int oxl = (e >> 3) & (a.TW - 1);
             if (oyl >= th || oxl >= tw) continue;
-            const int n = a.hcount[ox0 + oxl];
-            const float *t = s_tmp + (size_t)oyl * a.tmp_pitch + s_hl[oxl];
+            const int n = s_hn[oxl];
+            const float *t = s_tmp + oyl * a.tmp_pitch + s_hl[oxl];
             const float2 *wh = s_hw + oxl;
             float acc[C];
             if constexpr (!STRICT && C == 4) {
@@ -388,7 +406,7 @@ bool plan_tiles(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             p.tmp_pitch = tp;
             if (!direct) p.max_rows = std::max(p.max_rows, (TH * out_bytes_row + p.src_pitch - 1) / p.src_pitch);
             p.smem = (size_t)p.max_rows * p.src_pitch + (size_t)TH * p.tmp_pitch * 4 + (size_t)TH * vt.stride * 8 +
-                     (size_t)TW * ht.stride * 8 + (size_t)TW * 4 + 128;
+                     (size_t)TW * ht.stride * 8 + (size_t)(2 * TW + 2 * TH) * 4 + 128;
             if (p.smem > smem_budget) continue;
             // cost: staged bytes + intermediate work per destination pixel, with a mild
             // penalty for tiles so large that few CTAs fit per SM
@@ -575,6 +593,8 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     }
 
     a.TW = p.TW; a.TH = p.TH;
+    a.log2TW = 0;
+    while ((1 << a.log2TW) < p.TW) ++a.log2TW;
     a.tiles_x = (int)((nw + p.TW - 1) / p.TW);
     a.tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
     a.max_cols = p.max_cols; a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.tmp_pitch = p.tmp_pitch; a.out_pitch = p.out_pitch;
