@@ -31,6 +31,25 @@ def timed(fn, nbytes, label):
     print(f"{label:44s} {ms:8.3f} ms  {nbytes / ms / 1e6:8.1f} GB/s")
 
 
+# ---- resampler cases outside the bench line: f32 upscale (config 5 shape), u8 upscale, f32 downscale ----
+from image_b200 import FilterType
+def _resize_case(label, n_, w_, h_, c_, tdt, dt, nw_, nh_, filt):
+    if only and not only.search(label):
+        return
+    if tdt == torch.float32:
+        s_ = torch.rand((n_, h_, w_, c_), device=dev, generator=g)
+    else:
+        s_ = torch.randint(0, 256, (n_, h_, w_, c_), device=dev, generator=g).to(tdt)
+    d_ = torch.empty((n_, nh_, nw_, c_), dtype=tdt, device=dev)
+    for flags, tag in ((0, ""), (L.RESIZE_TILED, " [tile kernel]")):
+        timed(lambda: L.check(lib.b200img_resize_batch_dev(s_.data_ptr(), 0, w_, h_, c_, dt, d_.data_ptr(), 0, nw_, nh_, n_, int(filt), 1.0, flags, st)),
+              s_.numel() * s_.element_size() + d_.numel() * d_.element_size(), label + tag)
+_resize_case("resize f32 Rgba 8192x8192 -> 16384x16384 Lanczos3", 1, 8192, 8192, 4, torch.float32, L.F32, 16384, 16384, FilterType.Lanczos3)
+_resize_case("resize u8 Rgb 16x1920x1080 -> 2000x2000 Lanczos3", 16, 1920, 1080, 3, torch.uint8, L.U8, 2000, 2000, FilterType.Lanczos3)
+_resize_case("resize u8 Rgba 16x1920x1080 -> 3840x2160 CatmullRom", 16, 1920, 1080, 4, torch.uint8, L.U8, 3840, 2160, FilterType.CatmullRom)
+_resize_case("resize f32 Rgba 16x1920x1080 -> 960x540 Lanczos3", 16, 1920, 1080, 4, torch.float32, L.F32, 960, 540, FilterType.Lanczos3)
+_resize_case("resize u16 Rgb 16x1920x1080 -> 2560x1440 Triangle", 16, 1920, 1080, 3, torch.uint16, L.U16, 2560, 1440, FilterType.Triangle)
+
 n, w, h = 8, 3840, 2160
 # ---- either side of DynamicImage::resize: Rgba8 ----
 rgba = torch.randint(0, 256, (n * h, w, 4), device=dev, generator=g).to(torch.uint8)
