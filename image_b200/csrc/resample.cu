@@ -31,7 +31,8 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
                       float acc_init, bool strict, const DeviceCtx *ctx, cudaStream_t st);
 
 // resample_group.cu: tile kernel with four-sample groups on both axes (upscales, f32 images)
-int resize_group_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
+void resize_group_release(int device);
+int resize_group_try(int filter, uint32_t h, const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
                      size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t n_images,
                      const AxisTable &vt, const int32_t *d_vleft, const int32_t *d_vcount, const float *d_vw,
                      const AxisTable &ht, const int32_t *d_hleft, const int32_t *d_hcount, const float *d_hw,
@@ -579,7 +580,7 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
                                n_images, vt->host, vt->d_left, vt->d_count, vt->d_w, ht->host, ht->d_left, ht->d_count,
                                ht->d_w, acc_init, strict, ctx, st);
         if (rc != 0) return rc < 0 ? rc : B200IMG_OK;
-        rc = resize_group_try(src, a.src_img_stride, src_row0, w, C, dtype, dst, a.dst_img_stride, dst_row0, dst_rows, nw,
+        rc = resize_group_try(filter, h, src, a.src_img_stride, src_row0, w, C, dtype, dst, a.dst_img_stride, dst_row0, dst_rows, nw,
                               n_images, vt->host, vt->d_left, vt->d_count, vt->d_w, ht->host, ht->d_left, ht->d_count,
                               ht->d_w, acc_init, strict, ctx, st);
         if (rc != 0) return rc < 0 ? rc : B200IMG_OK;
@@ -619,6 +620,7 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
 }
 
 void resize_release_tables(int device) {
+    resize_group_release(device);
     std::lock_guard<std::mutex> lk(g_tab_mu);
     for (auto it = g_tabs.begin(); it != g_tabs.end();) {
         if (it->device == device) { free_table(*it); it = g_tabs.erase(it); }

@@ -20,6 +20,12 @@
 #include "host_tables.h"
 #include "packed.cuh"
 
+#include <cstdio>
+#include <cstdlib>
+#include <list>
+#include <mutex>
+#include <vector>
+
 namespace b200 {
 
 namespace {
@@ -43,6 +49,10 @@ struct GroupArgs {
     int tmp_pitch;             // floats per intermediate row
     int out_pitch;             // subpixels per staged output row
     int UV, UH;                // rows / pixels spanned by the windows of one group, at most
+    // per-axis group tables, built once per (filter, lengths) on the host: weights [group][U][GR]
+    // as (w, w) pairs, zero outside a sample's window; bu[group] = (first source index, span)
+    const float2 *vwt, *hwt;
+    const int2 *vbu, *hbu;
 };
 
 template <typename T, int C, bool STRICT>
@@ -55,10 +65,8 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
     float *s_tmp = reinterpret_cast<float *>(smem + a.src_bytes);                       // [TH][tmp_pitch]
     float2 *s_vwt = reinterpret_cast<float2 *>(s_tmp + a.TH * a.tmp_pitch);             // [TH/GR][UV][GR] (w, w)
     float2 *s_hwt = s_vwt + (a.TH / GR) * a.UV * GR;                                     // [TW/GR][UH][GR] (w, w)
-    int *s_vb = reinterpret_cast<int *>(s_hwt + (a.TW / GR) * a.UH * GR);               // [TH/GR] first staged row of a group
-    int *s_vu = s_vb + a.TH / GR;                                                        // [TH/GR] rows in its span
-    int *s_hb = s_vu + a.TH / GR;                                                        // [TW/GR] first float of a group's span in a tmp row
-    int *s_hu = s_hb + a.TW / GR;                                                        // [TW/GR] pixels in its span
+    int2 *s_vbu = reinterpret_cast<int2 *>(s_hwt + (a.TW / GR) * a.UH * GR);            // [TH/GR] (first source row, rows in the span)
+    int2 *s_hbu = s_vbu + a.TH / GR;                                                     // [TW/GR] (first source pixel, pixels in the span)
     __shared__ __align__(8) uint64_t bar;
 
     const int tid = threadIdx.x;
@@ -108,38 +116,20 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
         }
     }
 
-    // ---- group tables while the copies fly ----
+    // ---- this tile's slices of the group tables (16-byte async copies; groups are aligned to
+    // multiples of GR from sample 0, and so are tiles) ----
     const int vgroups = (th + GR - 1) / GR, hgroups = (tw + GR - 1) / GR;
-    for (int i = tid; i < vgroups * a.UV * GR; i += GK_THREADS) s_vwt[i] = make_float2(0.0f, 0.0f);
-    for (int i = tid; i < hgroups * a.UH * GR; i += GK_THREADS) s_hwt[i] = make_float2(0.0f, 0.0f);
-    for (int g = tid; g < vgroups; g += GK_THREADS) {
-        const int first = oy0 + g * GR, last = min(first + GR, oy0 + th) - 1;
-        s_vb[g] = a.vleft[first] - row0;
-        s_vu[g] = a.vleft[last] + a.vcount[last] - a.vleft[first];
+    {
+        const uint4 *gv = reinterpret_cast<const uint4 *>(a.vwt + (size_t)(oy0 / GR) * a.UV * GR);
+        const uint4 *gh = reinterpret_cast<const uint4 *>(a.hwt + (size_t)(ox0 / GR) * a.UH * GR);
+        const int nv = vgroups * a.UV * (GR / 2), nh = hgroups * a.UH * (GR / 2);
+        for (int i = tid; i < nv; i += GK_THREADS) cp_async(reinterpret_cast<uint4 *>(s_vwt) + i, gv + i, 16);
+        for (int i = tid; i < nh; i += GK_THREADS) cp_async(reinterpret_cast<uint4 *>(s_hwt) + i, gh + i, 16);
+        for (int g = tid; g < vgroups; g += GK_THREADS) s_vbu[g] = a.vbu[oy0 / GR + g];
+        for (int g = tid; g < hgroups; g += GK_THREADS) s_hbu[g] = a.hbu[ox0 / GR + g];
     }
-    for (int g = tid; g < hgroups; g += GK_THREADS) {
-        const int first = ox0 + g * GR, last = min(first + GR, ox0 + tw) - 1;
-        s_hb[g] = a.hleft[first] * C - sub0;
-        s_hu[g] = a.hleft[last] + a.hcount[last] - a.hleft[first];
-    }
-    __syncthreads();
-    // eight lanes walk the taps of one destination sample (no division per entry)
-    for (int o = tid >> 3; o < th; o += GK_THREADS / 8) {
-        const int g = o / GR, n = a.vcount[oy0 + o];
-        const int u0 = a.vleft[oy0 + o] - a.vleft[oy0 + g * GR];
-        const float *wsrc = a.vw + (size_t)(oy0 + o) * a.vstride;
-        float2 *wdst = s_vwt + (g * a.UV + u0) * GR + (o - g * GR);
-        for (int k = tid & 7; k < n; k += 8) { const float w = wsrc[k]; wdst[k * GR] = make_float2(w, w); }
-    }
-    for (int o = tid >> 3; o < tw; o += GK_THREADS / 8) {
-        const int g = o / GR, n = a.hcount[ox0 + o];
-        const int u0 = a.hleft[ox0 + o] - a.hleft[ox0 + g * GR];
-        const float *wsrc = a.hw + (size_t)(ox0 + o) * a.hstride;
-        float2 *wdst = s_hwt + (g * a.UH + u0) * GR + (o - g * GR);
-        for (int k = tid & 7; k < n; k += 8) { const float w = wsrc[k]; wdst[k * GR] = make_float2(w, w); }
-    }
+    cp_async_wait_all();
     if (rows16) mbar_wait(&bar, 0);
-    else cp_async_wait_all();
     __syncthreads();
 
     // ---- vertical pass: item = (row group g, unit x of a staged row); a warp's lanes are neighbouring
@@ -151,9 +141,10 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
         const int dy = GK_THREADS / units, dx = GK_THREADS - dy * units;
         int g = tid / units, x = tid - g * units;
         while (g < vgroups) {
-            const int U = s_vu[g];
+            const int2 bu = s_vbu[g];
+            const int U = bu.y;
             const float2 *wt = s_vwt + g * a.UV * GR;
-            const unsigned char *p = s_src + s_vb[g] * a.src_pitch + x * 16;
+            const unsigned char *p = s_src + (bu.x - row0) * a.src_pitch + x * 16;
             f32x2 a01[GR], a23[GR];
 #pragma unroll
             for (int k = 0; k < GR; ++k) { a01[k] = init2; a23[k] = init2; }
@@ -183,9 +174,10 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
         const int dy = GK_THREADS / units, dx = GK_THREADS - dy * units;
         int g = tid / units, x = tid - g * units;
         while (g < vgroups) {
-            const int U = s_vu[g];
+            const int2 bu = s_vbu[g];
+            const int U = bu.y;
             const float2 *wt = s_vwt + g * a.UV * GR;
-            const unsigned char *p = s_src + s_vb[g] * a.src_pitch + x * 4;
+            const unsigned char *p = s_src + (bu.x - row0) * a.src_pitch + x * 4;
             float *t = s_tmp + g * GR * a.tmp_pitch + x * N;
             if constexpr (PACKED && N == 4) {
                 f32x2 a01[GR], a23[GR];
@@ -274,8 +266,9 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
     for (int e = tid; e < (a.TW / GR) * a.TH; e += GK_THREADS) {
         const int row = e & (a.TH - 1), g = e >> a.log2TH;
         if (row >= th || g >= hgroups) continue;
-        const int U = s_hu[g];
-        const float *t = s_tmp + row * a.tmp_pitch + s_hb[g];
+        const int2 bu = s_hbu[g];
+        const int U = bu.y;
+        const float *t = s_tmp + row * a.tmp_pitch + (bu.x * C - sub0);
         const float2 *wt = s_hwt + g * a.UH * GR;
         float r[GR][C];
         if constexpr (PACKED && C == 4) {
@@ -394,20 +387,22 @@ int span_max(const AxisTable &t, uint32_t first, uint32_t count, int tile, int s
 struct GroupPlan { int TW, TH, max_rows, src_pitch, src_bytes, tmp_pitch, out_pitch, UV, UH; size_t smem; };
 
 bool plan_group(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, int C, int tsize,
-                size_t budget, GroupPlan *best) {
+                int UV, int UH, size_t budget, GroupPlan *best) {
     static const int tws[] = {16, 32, 64, 128};
     static const int ths[] = {16, 32, 64};
     double best_cost = 1e300;
     bool found = false;
+    int force_tw = 0, force_th = 0;
+    if (const char *e = getenv("B200IMG_GROUP_TILE")) sscanf(e, "%dx%d", &force_tw, &force_th);  // tuning aid
     for (int TW : tws)
         for (int TH : ths) {
+            if (force_tw && (TW != force_tw || TH != force_th)) continue;
             if ((TW / GR) * TH < GK_THREADS) continue;  // one horizontal item per thread at least
             GroupPlan p;
             p.TW = TW; p.TH = TH;
             const int max_cols = span_max(ht, 0, nw, TW, TW);
             p.max_rows = span_max(vt, dst_row0, dst_rows, TH, TH);
-            p.UV = span_max(vt, dst_row0, dst_rows, TH, GR);
-            p.UH = span_max(ht, 0, nw, TW, GR);
+            p.UV = UV; p.UH = UH;
             int out_bytes_row = round_up_g(TW * C * tsize, 16);
             if ((out_bytes_row / 16) % 2 == 0) out_bytes_row += 16;  // odd number of 16-byte units: lanes = rows write conflict-free
             p.out_pitch = out_bytes_row / tsize;
@@ -418,7 +413,7 @@ bool plan_group(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             const bool direct = C * tsize == 16;
             p.src_bytes = round_up_g(std::max(p.max_rows * p.src_pitch, direct ? 0 : TH * out_bytes_row), 128);
             p.smem = (size_t)p.src_bytes + (size_t)TH * tp * 4 + (size_t)TH * p.UV * 8 + (size_t)TW * p.UH * 8 +
-                     (size_t)(TH / GR + TW / GR) * 8 + 128;
+                     (size_t)(TH / GR + TW / GR) * 8 + 128;  // the last term: bu arrays
             if (p.smem > budget) continue;
             // cost per destination pixel: staged source bytes and vertical work (the intermediate is
             // max_cols wide), with a penalty when fewer than three CTAs fit an SM
@@ -431,6 +426,62 @@ bool plan_group(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             if (cost < best_cost) { best_cost = cost; *best = p; found = true; }
         }
     return found;
+}
+
+// ---- group tables, cached per (device, axis table identity) -----------------------------------
+// Built on the host from the axis table the caller already holds (same weights, regrouped):
+// wt[g][u][k] = weight of source sample first(g) + u for destination sample g*GR + k, as a (w, w)
+// pair; bu[g] = (first(g), span(g)).
+struct GroupTable {
+    int device = -1, filter = -1, axis = -1, U = 0;
+    uint32_t src_len = 0, dst_len = 0;
+    float2 *d_wt = nullptr;
+    int2 *d_bu = nullptr;
+};
+std::mutex g_gt_mu;
+std::list<GroupTable> g_gts;  // most recently used first
+constexpr size_t MAX_GROUP_TABLES = 32;
+
+int get_group_table(int device, int filter, int axis, uint32_t src_len, const AxisTable &t, uint32_t dst_len, int U,
+                    const GroupTable **out) {
+    std::lock_guard<std::mutex> lk(g_gt_mu);
+    for (auto it = g_gts.begin(); it != g_gts.end(); ++it)
+        if (it->device == device && it->filter == filter && it->axis == axis && it->src_len == src_len && it->dst_len == dst_len &&
+            it->U == U) {
+            g_gts.splice(g_gts.begin(), g_gts, it);
+            *out = &g_gts.front();
+            return B200IMG_OK;
+        }
+    const uint32_t groups = (dst_len + GR - 1) / GR;
+    std::vector<float2> wt((size_t)groups * U * GR, make_float2(0.0f, 0.0f));
+    std::vector<int2> bu(groups);
+    for (uint32_t g = 0; g < groups; ++g) {
+        const uint32_t first = g * GR, last = std::min<uint32_t>(first + GR, dst_len) - 1;
+        bu[g] = make_int2(t.left[first], t.left[last] + t.count[last] - t.left[first]);
+        for (uint32_t o = first; o <= last; ++o)
+            for (int k = 0; k < t.count[o]; ++k) {
+                const float w = t.w[(size_t)o * t.stride + k];
+                wt[((size_t)g * U + (t.left[o] + k - t.left[first])) * GR + (o - first)] = make_float2(w, w);
+            }
+    }
+    GroupTable gt;
+    gt.device = device; gt.filter = filter; gt.axis = axis; gt.src_len = src_len; gt.dst_len = dst_len; gt.U = U;
+    if (cudaMalloc(&gt.d_wt, wt.size() * sizeof(float2)) != cudaSuccess || cudaMalloc(&gt.d_bu, bu.size() * sizeof(int2)) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(gt.d_wt);
+        return fail(B200IMG_ERR_OOM, "resize: cannot allocate group tables");
+    }
+    // synchronous copies: complete before any stream can use them
+    B200_CUDA(cudaMemcpy(gt.d_wt, wt.data(), wt.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(gt.d_bu, bu.data(), bu.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    g_gts.push_front(gt);
+    if (g_gts.size() > MAX_GROUP_TABLES) {
+        cudaDeviceSynchronize();  // a queued kernel may still read the evicted table
+        cudaFree(g_gts.back().d_wt); cudaFree(g_gts.back().d_bu);
+        g_gts.pop_back();
+    }
+    *out = &g_gts.front();
+    return B200IMG_OK;
 }
 
 template <typename T, int C>
@@ -456,7 +507,15 @@ int launch_gt(const GroupArgs &a, int C, size_t smem, dim3 grid, bool strict, cu
 
 // Returns 1 if this kernel took the job (and launched it), 0 if it does not apply (the caller
 // falls back to resize_kernel), < 0 on error.
-int resize_group_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
+void resize_group_release(int device) {
+    std::lock_guard<std::mutex> lk(g_gt_mu);
+    for (auto it = g_gts.begin(); it != g_gts.end();) {
+        if (it->device == device) { cudaFree(it->d_wt); cudaFree(it->d_bu); it = g_gts.erase(it); }
+        else ++it;
+    }
+}
+
+int resize_group_try(int filter, uint32_t h, const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
                      size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t n_images,
                      const AxisTable &vt, const int32_t *d_vleft, const int32_t *d_vcount, const float *d_vw,
                      const AxisTable &ht, const int32_t *d_hleft, const int32_t *d_hcount, const float *d_hw,
@@ -464,12 +523,22 @@ int resize_group_try(const void *src, size_t src_img_stride, uint32_t src_row0, 
     if (dtype == B200IMG_F32 && strict) return 0;   // exact treatment of non-finite samples: resize_kernel
     if (vt.max_count < 2 && ht.max_count < 2) return 0;  // Nearest: one tap, nothing to share
     const int tsize = (int)dtype_size(dtype);
-    GroupPlan p;
-    const size_t budget = std::min<size_t>(ctx->smem_optin, 150 * 1024);
-    if (!plan_group(vt, ht, dst_row0, dst_rows, nw, C, tsize, budget, &p)) return 0;
+    // groups are aligned to multiples of GR from sample 0 (the tables are global): a band must start
+    // on a group boundary and end on one or at the image's last row
+    const uint32_t nh = (uint32_t)vt.left.size();
+    if (dst_row0 % GR != 0 || ((dst_row0 + dst_rows) % GR != 0 && dst_row0 + dst_rows != nh)) return 0;
+    const int UV = span_max(vt, 0, nh, nh, GR), UH = span_max(ht, 0, nw, nw, GR);
     // the union walk multiplies by zero outside a sample's own window: worth it only while the
     // unions stay close to the windows (upscales, moderate downscales of wide filters)
-    if (p.UV * 10 > vt.max_count * 13 + 10 || p.UH * 10 > ht.max_count * 13 + 10) return 0;  // union <= 1.3 x window + 1
+    if (UV * 10 > vt.max_count * 13 + 10 || UH * 10 > ht.max_count * 13 + 10) return 0;  // union <= 1.3 x window + 1
+    GroupPlan p;
+    const size_t budget = std::min<size_t>(ctx->smem_optin, 150 * 1024);
+    if (!plan_group(vt, ht, dst_row0, dst_rows, nw, C, tsize, UV, UH, budget, &p)) return 0;
+    const GroupTable *gv, *gh;
+    int rc = get_group_table(ctx->device, filter, 0, h, vt, nh, UV, &gv);
+    if (rc) return rc;
+    const float2 *vwt = gv->d_wt; const int2 *vbu = gv->d_bu;   // copied: the next call may reorder the cache
+    if ((rc = get_group_table(ctx->device, filter, 1, w, ht, nw, UH, &gh))) return rc;
     const int tiles_x = (int)((nw + p.TW - 1) / p.TW), tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
     if (tiles_y > 65535 || n_images > 65535) return 0;
 
@@ -484,8 +553,8 @@ int resize_group_try(const void *src, size_t src_img_stride, uint32_t src_row0, 
     while ((1 << a.log2TH) < p.TH) ++a.log2TH;
     a.max_rows = p.max_rows; a.src_pitch = p.src_pitch; a.src_bytes = p.src_bytes; a.tmp_pitch = p.tmp_pitch;
     a.out_pitch = p.out_pitch; a.UV = p.UV; a.UH = p.UH;
+    a.vwt = vwt; a.vbu = vbu; a.hwt = gh->d_wt; a.hbu = gh->d_bu;
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y, n_images);
-    int rc;
     if (dtype == B200IMG_U8) rc = launch_gt<uint8_t>(a, C, p.smem, grid, strict, st);
     else if (dtype == B200IMG_U16) rc = launch_gt<uint16_t>(a, C, p.smem, grid, strict, st);
     else rc = launch_gt<float>(a, C, p.smem, grid, strict, st);
