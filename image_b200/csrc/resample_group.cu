@@ -20,8 +20,6 @@
 #include "host_tables.h"
 #include "packed.cuh"
 
-#include <cstdio>
-#include <cstdlib>
 #include <list>
 #include <mutex>
 #include <vector>
@@ -392,11 +390,8 @@ bool plan_group(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
     static const int ths[] = {16, 32, 64};
     double best_cost = 1e300;
     bool found = false;
-    int force_tw = 0, force_th = 0;
-    if (const char *e = getenv("B200IMG_GROUP_TILE")) sscanf(e, "%dx%d", &force_tw, &force_th);  // tuning aid
     for (int TW : tws)
         for (int TH : ths) {
-            if (force_tw && (TW != force_tw || TH != force_th)) continue;
             if ((TW / GR) * TH < GK_THREADS) continue;  // one horizontal item per thread at least
             GroupPlan p;
             p.TW = TW; p.TH = TH;
