@@ -271,6 +271,20 @@ def extras(torch, lib, L, dev, stream, hbm, steps, warmup, FilterType, GaussianB
         k4.data_ptr(), 0, 1024, 1024, 4, L.U8, o4.data_ptr(), 0, 256, 256, n, int(FilterType.CatmullRom), 1.0, L.FP_FAST,
         stream)), n * 1024 * 1024 / 1e6, n * (1024 * 1024 * 4 + 256 * 256 * 4), "MP/s on source pixels")
     del k4, o4
+    # K5 shape on one GPU: 4096x4096 Rgba32F -> 8192x8192 Lanczos3 (268 MB in, 1.07 GB out)
+    k5 = torch.rand((1, 4096, 4096, 4), device=dev, generator=g)
+    o5 = torch.empty((1, 8192, 8192, 4), dtype=torch.float32, device=dev)
+    rec("resize_k5shape_lanczos3_rgba32f_4096_to_8192", lambda: L.check(lib.b200img_resize_batch_dev(
+        k5.data_ptr(), 0, 4096, 4096, 4, L.F32, o5.data_ptr(), 0, 8192, 8192, 1, int(FilterType.Lanczos3), 1.0, L.FP_FAST,
+        stream)), 4096 * 4096 / 1e6, (4096 * 4096 + 8192 * 8192) * 16, "MP/s on source pixels")
+    del k5, o5
+    # the first "next" row: thumbnail of 8 x 4K Rgb8 frames to 256x256
+    t8 = torch.randint(0, 256, (BATCH, H4K, W4K, 3), dtype=torch.uint8, device=dev, generator=g)
+    ot = torch.empty((BATCH, 256, 256, 3), dtype=torch.uint8, device=dev)
+    rec("thumbnail_8x4k_rgb8_to_256", lambda: L.check(lib.b200img_thumbnail_batch_dev(
+        t8.data_ptr(), W4K, H4K, 3, L.U8, ot.data_ptr(), 256, 256, BATCH, 0, stream)), BATCH * W4K * H4K / 1e6,
+        BATCH * (W4K * H4K * 3 + 256 * 256 * 3), "MP/s on source pixels")
+    del t8, ot
     # K3: conversions and swizzle at 8192x8192
     npx = 8192 * 8192
     a16 = torch.randint(0, 65536, (npx, 4), dtype=torch.int32, device=dev, generator=g).to(torch.uint16)
