@@ -47,6 +47,7 @@ def main():
         return resize_band(src, me, w, h, nw, nh, FilterType.Lanczos3, acc_init=a.acc_init)
 
     out = step()
+    out = step()   # twice: the caching allocator then holds both output buffers the timed loop alternates between
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
