@@ -63,7 +63,12 @@ typedef enum {
  * (f32) of the reference.  STRICT keeps every multiply and add separately
  * rounded, in the reference's order: bit-exact with a default x86-64 build of
  * the reference given the same libm.  Integer paths (conversions, swizzle,
- * Nearest, u8 box blur, Q0.15 Gaussian) are bit-exact under either flag. */
+ * Nearest, u8 box blur, Q0.15 Gaussian) are bit-exact under either flag.
+ * One more difference under FAST, for f32 images only: the resampler's grouped kernel walks the
+ * union of four neighbouring windows with zero weights outside each sample's own window, so a
+ * NON-FINITE source sample (0 * inf = NaN) can also turn up to three destination samples next to
+ * the ones whose windows contain it non-finite.  STRICT treats such samples exactly as the
+ * reference does. */
 #define B200IMG_FP_FAST 0
 #define B200IMG_FP_STRICT 1
 /* multiply_accumulate of the reference fuses when it is built with +fma or for
