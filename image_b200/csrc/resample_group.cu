@@ -261,10 +261,12 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
     const size_t d_pitch = (size_t)a.nw * C;
     T *gdst = dst + (size_t)(oy0 - (int)a.dst_row0) * d_pitch + (size_t)ox0 * C;
     const bool vec_dst = (sizeof(T) * d_pitch) % 16 == 0 && (reinterpret_cast<uintptr_t>(gdst) & 15) == 0;
-    for (int e = tid; e < (a.TW / GR) * a.TH; e += GK_THREADS) {
+    for (int e0 = 0; e0 < (a.TW / GR) * a.TH; e0 += GK_THREADS) {   // same trip count for every thread (barriers inside)
+        const int e = e0 + tid;
         const int row = e & (a.TH - 1), g = e >> a.log2TH;
-        if (row >= th || g >= hgroups) continue;
-        const int2 bu = s_hbu[g];
+        const bool valid = row < th && g < hgroups;
+        if (!DIRECT && !valid) continue;
+        const int2 bu = valid ? s_hbu[g] : make_int2(0, 0);
         const int U = bu.y;
         const float *t = s_tmp + row * a.tmp_pitch + (bu.x * C - sub0);
         const float2 *wt = s_hwt + g * a.UH * GR;
@@ -312,21 +314,37 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
         }
         constexpr int GBYTES = GR * C * (int)sizeof(T);
         if (DIRECT) {
-            // f32 x 4 channels: the group is 64 contiguous bytes = two full sectors; it goes straight to
-            // global memory (no staged tile: a third less shared memory)
-            T *o = gdst + (size_t)row * d_pitch + g * GR * C;
+            // f32 x 4 channels (16-byte pixels): the GK_THREADS items of this round are a block of
+            // BG = GK_THREADS / TH neighbouring column groups x TH rows.  It is transposed through the
+            // (now free) staged-source region so that a warp stores contiguous row segments: a
+            // lane-per-row store would cost one memory transaction per pixel.
+            const int BG = GK_THREADS >> a.log2TH;             // column groups in the block
+            const int seg = BG * GR;                            // pixels per row of the block
+            const int blk_pitch = seg * 16 + 16;                // bytes; odd number of 16-byte units
+            const int g_first = e0 >> a.log2TH;
+            if (valid) {
+                unsigned char *o = s_src + row * blk_pitch + (g - g_first) * (GR * 16);
 #pragma unroll
-            for (int k = 0; k < GR; ++k)
-                if (g * GR + k < tw) {
+                for (int k = 0; k < GR; ++k) {
                     T px[C];
 #pragma unroll
                     for (int c = 0; c < C; ++c) px[c] = Px<T>::clamp_nearest(r[k][c]);
-                    if (vec_dst) stg_stream(reinterpret_cast<uint4 *>(o + k * C), *reinterpret_cast<const uint4 *>(px));
-                    else {
-#pragma unroll
-                        for (int c = 0; c < C; ++c) o[k * C + c] = px[c];
-                    }
+                    *reinterpret_cast<uint4 *>(o + k * 16) = *reinterpret_cast<const uint4 *>(px);
                 }
+            }
+            __syncthreads();
+            const int px0 = g_first * GR;                       // first tile column of the block
+            const int lseg = 2 + 8 - a.log2TH;                  // log2(seg): GR = 4, GK_THREADS = 256
+            for (int v = tid; v < a.TH * seg; v += GK_THREADS) {
+                const int rr = v >> lseg, cc = v & (seg - 1);
+                if (rr < th && px0 + cc < tw) {
+                    const uint4 q = *reinterpret_cast<const uint4 *>(s_src + rr * blk_pitch + cc * 16);
+                    T *o = gdst + (size_t)rr * d_pitch + (size_t)(px0 + cc) * C;
+                    if (vec_dst) stg_stream(reinterpret_cast<uint4 *>(o), q);
+                    else { o[0] = __uint_as_float(q.x); o[1 % C] = __uint_as_float(q.y); o[2 % C] = __uint_as_float(q.z); o[3 % C] = __uint_as_float(q.w); }
+                }
+            }
+            __syncthreads();
             continue;
         }
         T *o = s_out + row * out_pitch + g * GR * C;
@@ -406,7 +424,9 @@ bool plan_group(const AxisTable &vt, const AxisTable &ht, uint32_t dst_row0, uin
             if ((tp / 4) % 2 == 0) tp += 4;                            // same for the intermediate rows
             p.tmp_pitch = tp;
             const bool direct = C * tsize == 16;
-            p.src_bytes = round_up_g(std::max(p.max_rows * p.src_pitch, direct ? 0 : TH * out_bytes_row), 128);
+            // the region also holds the staged output: the whole tile, or (16-byte pixels) one block of a round
+            const int blk_bytes = TH * ((GK_THREADS / TH) * GR * 16 + 16);
+            p.src_bytes = round_up_g(std::max(p.max_rows * p.src_pitch, direct ? blk_bytes : TH * out_bytes_row), 128);
             p.smem = (size_t)p.src_bytes + (size_t)TH * tp * 4 + (size_t)TH * p.UV * 8 + (size_t)TW * p.UH * 8 +
                      (size_t)(TH / GR + TW / GR) * 8 + 128;  // the last term: bu arrays
             if (p.smem > budget) continue;
