@@ -333,15 +333,26 @@ resize_group_kernel(const __grid_constant__ GroupArgs a) {
                 }
             }
             __syncthreads();
-            const int px0 = g_first * GR;                       // first tile column of the block
+            // the block is TH x seg pixels = 1024 16-byte vectors: four per thread, same column, rows
+            // GK_THREADS / seg apart
             const int lseg = 2 + 8 - a.log2TH;                  // log2(seg): GR = 4, GK_THREADS = 256
-            for (int v = tid; v < a.TH * seg; v += GK_THREADS) {
-                const int rr = v >> lseg, cc = v & (seg - 1);
-                if (rr < th && px0 + cc < tw) {
-                    const uint4 q = *reinterpret_cast<const uint4 *>(s_src + rr * blk_pitch + cc * 16);
-                    T *o = gdst + (size_t)rr * d_pitch + (size_t)(px0 + cc) * C;
-                    if (vec_dst) stg_stream(reinterpret_cast<uint4 *>(o), q);
-                    else { o[0] = __uint_as_float(q.x); o[1 % C] = __uint_as_float(q.y); o[2 % C] = __uint_as_float(q.z); o[3 % C] = __uint_as_float(q.w); }
+            const int cc = tid & (seg - 1), rstep = GK_THREADS >> lseg;
+            const int px = g_first * GR + cc;                   // tile column of this thread's vectors
+            if (px < tw) {
+                int rr = tid >> lseg;
+                const unsigned char *sp = s_src + rr * blk_pitch + cc * 16;
+                T *o = gdst + (size_t)rr * d_pitch + (size_t)px * C;
+                const size_t ostep = (size_t)rstep * d_pitch;
+                if (vec_dst) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k, rr += rstep, sp += rstep * blk_pitch, o += ostep)
+                        if (rr < th) stg_stream(reinterpret_cast<uint4 *>(o), *reinterpret_cast<const uint4 *>(sp));
+                } else {
+                    for (int k = 0; k < 4; ++k, rr += rstep, sp += rstep * blk_pitch, o += ostep)
+                        if (rr < th) {
+                            const uint4 q = *reinterpret_cast<const uint4 *>(sp);
+                            o[0] = __uint_as_float(q.x); o[1 % C] = __uint_as_float(q.y); o[2 % C] = __uint_as_float(q.z); o[3 % C] = __uint_as_float(q.w);
+                        }
                 }
             }
             __syncthreads();
