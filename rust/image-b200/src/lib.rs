@@ -159,6 +159,53 @@ pub mod imageops {
             out.as_mut_ptr() as *mut c_void, sigma, threshold as c_int, ffi::FP_FAST) });
         out
     }
+
+    // ---- colorops (src/imageops/colorops.rs); `f` is one of the elementwise entry points ----
+    fn colorop<I: GenericImageView>(image: &I, f: impl FnOnce(*const c_void, u32, u32, c_int, c_int, *mut c_void) -> c_int)
+        -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    {
+        let src = packed(image);
+        let mut out = ImageBuffer::new(image.width(), image.height());
+        check(f(src.as_ptr() as *const c_void, image.width(), image.height(), <I::Pixel as Pixel>::CHANNEL_COUNT as c_int,
+                <<I::Pixel as Pixel>::Subpixel as B200Subpixel>::DTYPE, out.as_mut_ptr() as *mut c_void));
+        out
+    }
+
+    /// `image::imageops::brighten` (colorops.rs:161).
+    pub fn brighten<I: GenericImageView>(image: &I, value: i32) -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    { colorop(image, |s, w, h, c, d, o| unsafe { ffi::b200img_brighten(s, w, h, c, d, o, value) }) }
+
+    /// `image::imageops::contrast` (colorops.rs:92).
+    pub fn contrast<I: GenericImageView>(image: &I, contrast: f32) -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    { colorop(image, |s, w, h, c, d, o| unsafe { ffi::b200img_contrast(s, w, h, c, d, o, contrast) }) }
+
+    /// `image::imageops::huerotate` (colorops.rs:232).
+    pub fn huerotate<I: GenericImageView>(image: &I, value: i32) -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel
+    { colorop(image, |s, w, h, c, d, o| unsafe { ffi::b200img_huerotate(s, w, h, c, d, o, value) }) }
+
+    /// `image::imageops::invert` (colorops.rs:70): in place.
+    pub fn invert<P: Pixel>(image: &mut ImageBuffer<P, Vec<P::Subpixel>>)
+    where P::Subpixel: B200Subpixel
+    {
+        let (w, h) = image.dimensions();
+        let p = image.as_mut_ptr() as *mut c_void;
+        check(unsafe { ffi::b200img_invert(p as *const c_void, w, h, P::CHANNEL_COUNT as c_int, <P::Subpixel as B200Subpixel>::DTYPE, p) });
+    }
+
+    /// `has_constant_alpha` of `resize_impl` (src/imageops/resize.rs:155).
+    pub fn has_constant_alpha<P: Pixel>(image: &ImageBuffer<P, Vec<P::Subpixel>>) -> bool
+    where P::Subpixel: B200Subpixel
+    {
+        let (w, h) = image.dimensions();
+        let mut r: c_int = 1;
+        check(unsafe { ffi::b200img_has_constant_alpha(image.as_ptr() as *const c_void, w, h, P::CHANNEL_COUNT as c_int,
+            <P::Subpixel as B200Subpixel>::DTYPE, &mut r) });
+        r != 0
+    }
 }
 
 /// `ImageBuffer::convert::<To>()` (src/images/buffer.rs:1643): FromColor arithmetic.
