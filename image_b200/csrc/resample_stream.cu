@@ -337,6 +337,13 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
     const size_t gp = (size_t)w * C * tsize;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
     if (vt.max_count < 2) return 0;  // Nearest: nothing to share between rows; the tile kernel is fine
+    // vertical upscales belong to the tile kernels: many destination rows per source row would fill the
+    // accumulator slots with windows that overlap almost entirely (measured: Triangle 1080 -> 2000 rows
+    // took 83 us here against 49 us in the tile kernel)
+    {
+        const size_t nh_all = vt.left.size();
+        if (nh_all && (size_t)(vt.left[nh_all - 1] + vt.count[nh_all - 1]) < nh_all) return 0;
+    }
     // a quick reject for upscales before the exact count below
     if ((uint64_t)vt.left.size() > 0 && dst_rows > 12 && vt.left[dst_row0 + 12] - vt.left[dst_row0] < 1) return 0;
 
@@ -352,6 +359,9 @@ int resize_stream_try(const void *src, size_t src_img_stride, uint32_t src_row0,
     while (BAND > 16 && (uint64_t)strips * ((dst_rows + BAND - 1) / BAND) * n_images < (uint64_t)ctx->sm_count * 6) BAND /= 2;
     const int bands = (int)((dst_rows + BAND - 1) / BAND);
     if (bands > 65535 || n_images > 65535) return 0;
+    // a single small image does not give this kernel one CTA per SM even with 16-row bands: the tile
+    // kernels spread it better (1080p -> 400x300: 23-26 us here, 15-23 us there)
+    if ((uint64_t)strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;
     const int A = slots_needed(vt, dst_row0, dst_rows, BAND);
     if (A == 0) return 0;
     int max_band_rows = 1;

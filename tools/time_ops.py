@@ -48,6 +48,10 @@ _resize_case("resize f32 Rgba 8192x8192 -> 16384x16384 Lanczos3", 1, 8192, 8192,
 _resize_case("resize u8 Rgb 16x1920x1080 -> 2000x2000 Lanczos3", 16, 1920, 1080, 3, torch.uint8, L.U8, 2000, 2000, FilterType.Lanczos3)
 _resize_case("resize u8 Rgba 16x1920x1080 -> 3840x2160 CatmullRom", 16, 1920, 1080, 4, torch.uint8, L.U8, 3840, 2160, FilterType.CatmullRom)
 _resize_case("resize f32 Rgba 16x1920x1080 -> 960x540 Lanczos3", 16, 1920, 1080, 4, torch.float32, L.F32, 960, 540, FilterType.Lanczos3)
+# the reference's own bench shapes (benches/imageops.rs:95-124), one image per call
+for _f in (FilterType.Nearest, FilterType.Triangle, FilterType.CatmullRom, FilterType.Gaussian, FilterType.Lanczos3):
+    _resize_case(f"resize u8 Rgb 1x1920x1080 -> 400x300 {_f.name}", 1, 1920, 1080, 3, torch.uint8, L.U8, 400, 300, _f)
+    _resize_case(f"resize u8 Rgb 1x1920x1080 -> 2000x2000 {_f.name}", 1, 1920, 1080, 3, torch.uint8, L.U8, 2000, 2000, _f)
 _resize_case("resize u16 Rgb 16x1920x1080 -> 2560x1440 Triangle", 16, 1920, 1080, 3, torch.uint16, L.U16, 2560, 1440, FilterType.Triangle)
 
 n, w, h = 8, 3840, 2160
