@@ -22,7 +22,7 @@
 namespace b200 {
 
 // gauss_tiled.cu: register-tiled passes for reorderable sums (FAST f32 engine, Q0.15 engine)
-constexpr int GT_MAX_TAPS = 128;
+constexpr int GT_MAX_TAPS = 384;
 template <typename T, typename Mid, typename Acc>
 int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
                     const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
@@ -172,16 +172,22 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
     const bool strict = (flags & B200IMG_FP_STRICT) != 0;
     if ((q15 || !strict) && rk.size() <= (size_t)GT_MAX_TAPS && ck.size() <= (size_t)GT_MAX_TAPS) {
         const int rl = (int)rk.size(), cl = (int)ck.size();
-#define TILED(T, Mid, Acc) \
-    return gauss_tiled_run<T, Mid, Acc>((const T *)src, (T *)dst, (Mid *)mid, w, h, C, n_images, rk.data(), rl, ck.data(), cl, \
-                                        g.row_shift, g.zero_first_row, st)
-        if (q15) {
-            if (dtype == B200IMG_U8) TILED(uint8_t, uint8_t, uint32_t);
-            TILED(uint16_t, uint16_t, uint32_t);
-        }
-        if (dtype == B200IMG_U8) TILED(uint8_t, float, float);
-        if (dtype == B200IMG_U16) TILED(uint16_t, float, float);
-        TILED(float, float, float);
+#define TILED(T, Mid, Acc)                                                                                                  \
+    {                                                                                                                      \
+        const int tr = gauss_tiled_run<T, Mid, Acc>((const T *)src, (T *)dst, (Mid *)mid, w, h, C, n_images, rk.data(), rl, \
+                                                    ck.data(), cl, g.row_shift, g.zero_first_row, st);                     \
+        if (tr != 1) return tr; /* 1 = tile too large for shared memory: direct kernels below */                           \
+        break;                                                                                                             \
+    }
+        do {
+            if (q15) {
+                if (dtype == B200IMG_U8) TILED(uint8_t, uint8_t, uint32_t)
+                TILED(uint16_t, uint16_t, uint32_t)
+            }
+            if (dtype == B200IMG_U8) TILED(uint8_t, float, float)
+            if (dtype == B200IMG_U16) TILED(uint16_t, float, float)
+            TILED(float, float, float)
+        } while (0);
 #undef TILED
     }
 

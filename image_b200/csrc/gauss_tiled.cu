@@ -26,7 +26,7 @@
 namespace b200 {
 
 constexpr int GT_R = 8;           // outputs per thread along the filter axis
-constexpr int GT_MAX_TAPS = 128;  // longer kernels take the direct kernels in gauss.cu
+constexpr int GT_MAX_TAPS = 384;  // longer kernels (sigma > 57) take the direct kernels in gauss.cu
 constexpr int GT_THREADS = 256;
 
 struct TapWeights { uint32_t w[GT_MAX_TAPS]; };  // f32 bits or Q0.15 integers, zero padded
@@ -409,7 +409,8 @@ col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
 
 }  // namespace
 
-// Launches both passes.  rk / ck are the scanned kernels (f32 bits or Q0.15), lengths odd <= 128.
+// Launches both passes.  rk / ck are the scanned kernels (f32 bits or Q0.15), lengths odd <= GT_MAX_TAPS.
+// Returns 1 (nothing launched) when a pass's tile does not fit shared memory: the caller falls back.
 template <typename T, typename Mid, typename Acc>
 int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int C, uint32_t n_images,
                     const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
@@ -438,6 +439,8 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
     const size_t row_smem_int = (size_t)ROW_ROWS * (in_pitch + out_pitch) * 4;
     const size_t row_smem = (size_t)ROW_ROWS * std::max(in_pitch, out_pitch) * 4;  // f32 kernels alias the two
     const size_t col_smem = (size_t)(COL_TH + cnch * ctc - 1) * COL_TW * 4;
+    constexpr size_t SMEM_MAX = 227 * 1024;  // per-CTA opt-in limit on sm_100
+    if ((F32X2 ? row_smem : row_smem_int) > SMEM_MAX || col_smem > SMEM_MAX) return 1;
     const dim3 row_grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
     const dim3 col_grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
 

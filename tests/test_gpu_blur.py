@@ -156,3 +156,16 @@ def test_host_batch_entry_points_match_single_calls(cuda):
     L.check(lib.b200img_fast_blur_batch(big.ctypes.data, 300, 200, 4, L.U8, outb.ctypes.data, 4, 5.0))
     for i in range(4):
         assert np.array_equal(outb[i], o.fast_blur(big[i], 5.0)), i
+
+
+@pytest.mark.parametrize("dtype", DT)
+def test_long_kernels(cuda, dtype):
+    """benches/blur.rs uses sigma = 50 (331 taps): the tiled kernels take kernels up to 384 taps, the
+    direct kernels everything beyond (sigma = 60: 397 taps) and tiles that do not fit shared memory"""
+    rng = np.random.default_rng(31)
+    for c in (1, 3, 4):
+        img = rand_image(rng, 70, 90, c, dtype)
+        _gauss_check(img, GaussianBlurParameters.new_from_sigma(50.0), cuda)
+    img = rand_image(rng, 40, 50, 3, dtype)
+    _gauss_check(img, GaussianBlurParameters.new_from_sigma(60.0), cuda)
+    _gauss_check(img, GaussianBlurParameters.new_anisotropic_kernel_size(301.0, 5.0), cuda)

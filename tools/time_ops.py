@@ -54,6 +54,19 @@ for _f in (FilterType.Nearest, FilterType.Triangle, FilterType.CatmullRom, Filte
     _resize_case(f"resize u8 Rgb 1x1920x1080 -> 2000x2000 {_f.name}", 1, 1920, 1080, 3, torch.uint8, L.U8, 2000, 2000, _f)
 _resize_case("resize u16 Rgb 16x1920x1080 -> 2560x1440 Triangle", 16, 1920, 1080, 3, torch.uint16, L.U16, 2560, 1440, FilterType.Triangle)
 
+# ---- the reference's blur bench shapes (benches/blur.rs): one 1024x768 Rgb8 image, sigma 3 / 7 / 50 ----
+from image_b200 import GaussianBlurParameters
+import ctypes as C
+_b = torch.randint(0, 256, (768, 1024, 3), device=dev, generator=g).to(torch.uint8)
+_bo = torch.empty_like(_b)
+for _s in (3.0, 7.0, 50.0):
+    _p = GaussianBlurParameters.new_from_sigma(_s)
+    timed(lambda: L.check(lib.b200img_fast_blur_dev(_b.data_ptr(), 1024, 768, 3, L.U8, _bo.data_ptr(), _s, st)), 2 * _b.numel(), f"refbench fast_blur 1024x768 Rgb8 sigma {_s:g}")
+    timed(lambda: L.check(lib.b200img_gaussian_blur_dev(_b.data_ptr(), 1024, 768, 3, L.U8, _bo.data_ptr(), C.byref(_p.raw), L.BLUR_GENERIC, 0, st)),
+          2 * _b.numel(), f"refbench blur_advanced 1024x768 Rgb8 sigma {_s:g} ({_p.raw.x_kernel_size} taps)")
+    timed(lambda: L.check(lib.b200img_gaussian_blur_dev(_b.data_ptr(), 1024, 768, 3, L.U8, _bo.data_ptr(), C.byref(_p.raw), L.BLUR_DYN, 0, st)),
+          2 * _b.numel(), f"refbench DynamicImage::blur_advanced 1024x768 Rgb8 sigma {_s:g}")
+
 n, w, h = 8, 3840, 2160
 # ---- either side of DynamicImage::resize: Rgba8 ----
 rgba = torch.randint(0, 256, (n * h, w, 4), device=dev, generator=g).to(torch.uint8)
