@@ -21,8 +21,8 @@ namespace b200 {
 namespace {
 
 constexpr int V_THREADS = 256;
-constexpr int V_BAND = 64;
-constexpr int H_THREADS = 128;
+constexpr int V_BAND = 64;       // rows per CTA band of the vertical pass (halved for small jobs, see box_pass_u8)
+constexpr int H_THREADS = 128;   // 4 warps = the 4 chunks of a tile; small jobs run 16-pixel chunks on 16 warps
 constexpr int H_ROWS = 32;
 constexpr int H_XT = 256;
 constexpr int H_XC = 64;
@@ -38,11 +38,11 @@ __device__ __forceinline__ uint32_t byte_of(uint32_t w, int j) { return __byte_p
 
 // ---- vertical ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(V_THREADS)
-box_v_u8_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, U8Geom g, uint32_t words, int bands) {
+box_v_u8_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, U8Geom g, uint32_t words, int bands, int vband) {
     const uint32_t wd = blockIdx.x * V_THREADS + threadIdx.x;
     if (wd >= words) return;
     const uint32_t img = blockIdx.y / bands, band = blockIdx.y % bands;
-    const int y0 = (int)band * V_BAND, y1 = min(y0 + V_BAND, (int)g.h);
+    const int y0 = (int)band * vband, y1 = min(y0 + vband, (int)g.h);
     const int r = (int)g.r, hmax = (int)g.h - 1;
     const uint32_t *p = src + (size_t)img * g.h * words + wd;
     uint32_t *d = dst + (size_t)img * g.h * words + wd;
@@ -97,9 +97,10 @@ box_v_u8_kernel(const uint32_t *__restrict__ src, uint32_t *__restrict__ dst, U8
 
 // ---- horizontal ----------------------------------------------------------------------------------
 template <int C>
-__global__ void __launch_bounds__(H_THREADS)
+__global__ void __launch_bounds__(512)
 box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Geom g, size_t total_rows, int in_pitch,
-                int out_pitch) {
+                int out_pitch, int xc) {
+    const int nwarps = blockDim.x >> 5;   // = H_XT / xc
     extern __shared__ __align__(16) uint32_t sm[];
     uint32_t *s_in = sm;                                 // [H_ROWS][in_pitch] words; staged pixel 0 = source pixel x0 - r
     uint32_t *s_out = sm + (size_t)H_ROWS * in_pitch;    // [H_ROWS][out_pitch] words; pixel 0 = x0
@@ -122,7 +123,7 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
         phase = (int)(reinterpret_cast<uintptr_t>(gb0) & 3);
     }
     const int swords = (phase + sbytes + 3) / 4;
-    for (int rr = warp; rr < H_ROWS; rr += H_THREADS / 32) {
+    for (int rr = warp; rr < H_ROWS; rr += nwarps) {
         const uint8_t *grow = src + min(row0 + rr, total_rows - 1) * g_pitch;
         uint32_t *s = s_in + (size_t)rr * in_pitch;
         if (interior) {
@@ -143,13 +144,13 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
     __syncthreads();
 
     // lane = row; item = 64-pixel chunk; steps of 4 pixels = C words
-    const int chunks = (tw + H_XC - 1) / H_XC;
+    const int chunks = (tw + xc - 1) / xc;
     const uint32_t *in_row = s_in + (size_t)lane * in_pitch;
     uint32_t *out_row = s_out + (size_t)lane * out_pitch;
     const int pshift = phase * 8;                                // outgoing pixels: byte phase of the staged row
     const int nbyte = ((2 * r + 1) * C + phase) & 3;             // incoming pixels: phase + window offset
-    for (int ck = warp; ck < chunks; ck += H_THREADS / 32) {
-        const int xa = ck * H_XC, xb = min(xa + H_XC, tw);
+    for (int ck = warp; ck < chunks; ck += nwarps) {
+        const int xa = ck * xc, xb = min(xa + xc, tw);
         uint32_t sum[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) sum[c] = g.bias;
@@ -191,7 +192,7 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
     __syncthreads();
 
     const int obytes = tw * C;
-    for (int rr = warp; rr < H_ROWS; rr += H_THREADS / 32) {
+    for (int rr = warp; rr < H_ROWS; rr += nwarps) {
         const size_t row = row0 + rr;
         if (row >= total_rows) break;
         uint8_t *gout = dst + row * g_pitch + (size_t)x0 * C;  // 4-byte aligned: g_pitch % 4 == 0, x0 % 4 == 0
@@ -226,11 +227,16 @@ int box_pass_u8(const uint8_t *src, uint8_t *tmp, uint8_t *dst, uint32_t w, uint
         const size_t smem = (size_t)H_ROWS * (in_pitch + out_pitch) * 4;
         if (smem > ctx->smem_optin) return 0;
         const dim3 grid((w + H_XT - 1) / H_XT, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
+        // a job too small to give every SM two 4-warp CTAs runs 16-pixel chunks on 16 warps per CTA: each
+        // chunk re-primes its window (2r + 1 pixels), which is cheaper than idle SMs
+        const bool small = (uint64_t)grid.x * grid.y < 2ull * ctx->sm_count;
+        const int xc = small ? 16 : H_XC;
+        const int hthreads = 32 * (H_XT / xc);
 #define H_GO(CC)                                                                                        \
     {                                                                                                   \
         auto k = box_h_u8_kernel<CC>;                                                                   \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
-        k<<<grid, H_THREADS, smem, st>>>(src, tmp, g, total_rows, in_pitch, out_pitch);                 \
+        k<<<grid, hthreads, smem, st>>>(src, tmp, g, total_rows, in_pitch, out_pitch, xc);              \
     }
         switch (C) {
             case 1: H_GO(1) break;
@@ -242,10 +248,14 @@ int box_pass_u8(const uint8_t *src, uint8_t *tmp, uint8_t *dst, uint32_t w, uint
     }
     {
         const uint32_t words = (uint32_t)(row_bytes / 4);
-        const int bands = (int)((h + V_BAND - 1) / V_BAND);
+        // shorter bands (each re-primes its 2r + 1 row window) until every SM has two CTAs
+        int vband = V_BAND;
+        const uint64_t per_band = (uint64_t)((words + V_THREADS - 1) / V_THREADS) * n_images;
+        while (vband > 8 && per_band * ((h + vband - 1) / vband) < 2ull * ctx->sm_count) vband /= 2;
+        const int bands = (int)((h + vband - 1) / vband);
         const dim3 grid((words + V_THREADS - 1) / V_THREADS, (unsigned)(bands * n_images));
         box_v_u8_kernel<<<grid, V_THREADS, 0, st>>>(reinterpret_cast<const uint32_t *>(tmp), reinterpret_cast<uint32_t *>(dst), g,
-                                                     words, bands);
+                                                     words, bands, vband);
     }
     B200_CUDA(cudaGetLastError());
     return 1;
