@@ -97,9 +97,44 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm(
 // acc[r] = (sum_k A[(r+k)*STRIDE] w[k], sum_k B[(r+k)*STRIDE] w[k]), k < nch * TC.  PAIRED: B = A + 1
 // and A is 8-byte aligned, so one LDS.64 fetches both.  TC (taps per unrolled chunk) is chosen per
 // launch from {5,6,7,8} to minimise zero-padded taps (65 taps = 13 x 5, 21 = 3 x 7).
-template <int STRIDE, bool PAIRED, int TC>
+// The window lives in a register RING of RS = TC * U entries (the smallest multiple of TC that
+// holds GT_R - 1 + TC of them); the chunk loop is unrolled U times, so ring positions are
+// compile-time constants and sliding the window by TC costs no register moves (sliding a linear
+// window cost 14 moves per 40 FFMA2 in loops that are issue-bound).
+// RING = false keeps a linear window and moves it (fewer registers, less code): measured faster for
+// short kernels (21 taps), the ring for long ones (65 taps); the launcher picks by chunk count.
+template <int STRIDE, bool PAIRED, int TC, bool RING>
 __device__ __forceinline__ void conv8x2(const float *inA, const float *inB, int nch, const TapWeights2 &tw, f32x2 (&acc)[GT_R]) {
-    f32x2 win[GT_R - 1 + TC];
+    if constexpr (!RING) {
+        f32x2 win[GT_R - 1 + TC];
+        auto ld = [&](int i) -> f32x2 {
+            if constexpr (PAIRED) return *reinterpret_cast<const f32x2 *>(inA + i * STRIDE);
+            else return pack2(inA[i * STRIDE], inB[i * STRIDE]);
+        };
+#pragma unroll
+        for (int i = 0; i < GT_R - 1; ++i) win[i] = ld(i);
+        inA += (GT_R - 1) * STRIDE;
+        inB += (GT_R - 1) * STRIDE;
+#pragma unroll 1
+        for (int ch = 0; ch < nch; ++ch) {
+#pragma unroll
+            for (int i = 0; i < TC; ++i) win[GT_R - 1 + i] = ld(i);
+            inA += TC * STRIDE;
+            inB += TC * STRIDE;
+#pragma unroll
+            for (int kk = 0; kk < TC; ++kk) {
+                const f32x2 wk = tw.w[ch * TC + kk];
+#pragma unroll
+                for (int r = 0; r < GT_R; ++r) acc[r] = fma2(win[r + kk], wk, acc[r]);
+            }
+#pragma unroll
+            for (int i = 0; i < GT_R - 1; ++i) win[i] = win[TC + i];
+        }
+        return;
+    }
+    constexpr int U = (GT_R - 1 + TC + TC - 1) / TC;
+    constexpr int RS = TC * U;
+    f32x2 win[RS];
     auto ld = [&](int i) -> f32x2 {
         if constexpr (PAIRED) return *reinterpret_cast<const f32x2 *>(inA + i * STRIDE);
         else return pack2(inA[i * STRIDE], inB[i * STRIDE]);
@@ -109,19 +144,22 @@ __device__ __forceinline__ void conv8x2(const float *inA, const float *inB, int 
     inA += (GT_R - 1) * STRIDE;
     inB += (GT_R - 1) * STRIDE;
 #pragma unroll 1
-    for (int ch = 0; ch < nch; ++ch) {
+    for (int ch = 0; ch < nch; ch += U) {
 #pragma unroll
-        for (int i = 0; i < TC; ++i) win[GT_R - 1 + i] = ld(i);
-        inA += TC * STRIDE;
-        inB += TC * STRIDE;
+        for (int u = 0; u < U; ++u) {
+            if (ch + u < nch) {  // chunk ch + u: logical window entry i sits at ring position (u * TC + i) mod RS
 #pragma unroll
-        for (int kk = 0; kk < TC; ++kk) {
-            const f32x2 wk = tw.w[ch * TC + kk];
+                for (int i = 0; i < TC; ++i) win[(u * TC + GT_R - 1 + i) % RS] = ld(i);
+                inA += TC * STRIDE;
+                inB += TC * STRIDE;
 #pragma unroll
-            for (int r = 0; r < GT_R; ++r) acc[r] = fma2(win[r + kk], wk, acc[r]);
+                for (int kk = 0; kk < TC; ++kk) {
+                    const f32x2 wk = tw.w[(ch + u) * TC + kk];
+#pragma unroll
+                    for (int r = 0; r < GT_R; ++r) acc[r] = fma2(win[(u * TC + r + kk) % RS], wk, acc[r]);
+                }
+            }
         }
-#pragma unroll
-        for (int i = 0; i < GT_R - 1; ++i) win[i] = win[TC + i];
     }
 }
 
@@ -150,6 +188,48 @@ __device__ __forceinline__ void stage_convert_row(const In *g, float *s, int n, 
             }
         }
     }
+}
+
+// The same for the NR rows a warp stages, with every global load of the warp issued before the first
+// conversion: one row at a time leaves each load's DRAM latency exposed (the row pass spent 45 % of its
+// stall samples in that loop).  Rows are `g_pitch` elements apart in global memory, `s_pitch` floats apart
+// in shared memory; all rows have the same byte phase (row pitch is a multiple of 4 bytes).  Returns false
+// (nothing done) when a row has more than 32 * MAXIT words.
+template <typename In, int NR, int MAXIT>
+__device__ __forceinline__ bool stage_convert_rows(const In *const (&g)[NR], float *const (&s)[NR], int n, int lane) {
+    static_assert(sizeof(In) < 4, "integer subpixels only");
+    constexpr int PER = 4 / sizeof(In);
+    const int phase = (int)((reinterpret_cast<uintptr_t>(g[0]) & 3) / sizeof(In));
+    const int words = (phase + n + PER - 1) / PER;
+    if (words > 32 * MAXIT) return false;
+    uint32_t wv[NR][MAXIT];
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const uint32_t *gw = reinterpret_cast<const uint32_t *>(g[r] - phase);
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int wi = it * 32 + lane;
+            wv[r][it] = wi < words ? __ldg(gw + wi) : 0u;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+#pragma unroll
+        for (int it = 0; it < MAXIT; ++it) {
+            const int wi = it * 32 + lane;
+            if (wi < words) {
+                const int e0 = wi * PER - phase;
+#pragma unroll
+                for (int j = 0; j < PER; ++j) {
+                    const int e = e0 + j;
+                    uint32_t m;
+                    if constexpr (PER == 4) m = __byte_perm(wv[r][it], 0x4B000000u, 0x7540 + j);
+                    else m = __byte_perm(wv[r][it], 0x4B000000u, j == 0 ? 0x7510 : 0x7532);
+                    if (e >= 0 && e < n) s[r][e] = __uint_as_float(m) - 8388608.0f;
+                }
+            }
+        }
+    return true;
 }
 
 constexpr int ROW_XT = 64;    // output pixels per CTA tile (row pass)
@@ -275,7 +355,7 @@ template <> struct StF<uint8_t, true> {
 };
 
 // Row pass: lane = row, warp item = (pixel blocks xb and xb + 4, channel): 16 outputs per thread.
-template <typename In, typename Mid, int C, bool Q15, int TC>
+template <typename In, typename Mid, int C, bool Q15, int TC, bool RING>
 __global__ void __launch_bounds__(GT_THREADS)
 row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, size_t total_rows, int half,
                  int shift, int nch, int in_pitch, const __grid_constant__ TapWeights2 tw) {
@@ -292,7 +372,22 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
     const bool interior = xs >= 0 && xs + sp <= (int)W;
     const bool words_ok = (g_pitch * sizeof(In)) % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
 
-    for (int r = warp; r < ROW_ROWS; r += GT_THREADS / 32) {
+    bool staged = false;
+    if constexpr (sizeof(In) < 4) {
+        if (interior && words_ok) {  // the warp's four rows at once, all loads in flight together
+            constexpr int NR = ROW_ROWS / (GT_THREADS / 32);
+            const In *gr[NR];
+            float *sr[NR];
+#pragma unroll
+            for (int k = 0; k < NR; ++k) {
+                const int r = warp + k * (GT_THREADS / 32);
+                gr[k] = src + min(row0 + r, total_rows - 1) * g_pitch + (size_t)xs * C;
+                sr[k] = s_in + r * in_pitch;
+            }
+            staged = stage_convert_rows<In, NR, 5>(gr, sr, row_elems, lane);
+        }
+    }
+    for (int r = warp; r < ROW_ROWS && !staged; r += GT_THREADS / 32) {
         const In *g = src + min(row0 + r, total_rows - 1) * g_pitch;
         float *s = s_in + r * in_pitch;
         if (interior && words_ok) {
@@ -321,7 +416,7 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
         if (item < ITEMS) {
             const int xb = item / C, c = item - xb * C;
             const float *a = s_in + lane * in_pitch + (xb * GT_R) * C + c;
-            conv8x2<C, false, TC>(a, a + HALF_BLOCKS * GT_R * C, nch, tw, acc[it]);
+            conv8x2<C, false, TC, RING>(a, a + HALF_BLOCKS * GT_R * C, nch, tw, acc[it]);
         }
     }
     __syncthreads();
@@ -350,7 +445,7 @@ row_f32x2_kernel(const In *__restrict__ src, Mid *__restrict__ mid, uint32_t W, 
 }
 
 // Column pass: thread = two adjacent subpixel columns x 8 rows; one LDS.64 per staged row.
-template <typename Mid, typename Out, bool Q15, int TC>
+template <typename Mid, typename Out, bool Q15, int TC, bool RING>
 __global__ void __launch_bounds__(GT_THREADS)
 col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t row_sub, uint32_t H, int tiles_y, int half,
                  int nch, int zero_first_row, const __grid_constant__ TapWeights2 tw) {
@@ -391,7 +486,7 @@ col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) acc[r] = 0ull;
         const float *a = s + (rb * GT_R) * COL_TW + 2 * cp;
-        conv8x2<COL_TW, true, TC>(a, a + 1, nch, tw, acc);
+        conv8x2<COL_TW, true, TC, RING>(a, a + 1, nch, tw, acc);
         const uint32_t col = s0 + 2 * cp;
 #pragma unroll
         for (int r = 0; r < GT_R; ++r) {
@@ -444,6 +539,7 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
     const dim3 row_grid((w + ROW_XT - 1) / ROW_XT, (unsigned)((total_rows + ROW_ROWS - 1) / ROW_ROWS));
     const dim3 col_grid((row_sub + COL_TW - 1) / COL_TW, (unsigned)(tiles_y * n_images));
 
+    constexpr int RING_MIN_CHUNKS = 6;  // ring-window kernels from this many tap chunks on (see conv8x2)
     if constexpr (F32X2) {
         TapWeights2 rwl, cwl;
         for (int i = 0; i < GT_MAX_TAPS; ++i) {
@@ -458,7 +554,7 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
         }
 #define ROW_GO2(CC, TCC)                                                                                             \
     {                                                                                                                \
-        auto k = row_f32x2_kernel<T, Mid, CC, Q15F, TCC>;                                                            \
+        auto k = rnch >= RING_MIN_CHUNKS ? row_f32x2_kernel<T, Mid, CC, Q15F, TCC, true> : row_f32x2_kernel<T, Mid, CC, Q15F, TCC, false>; \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)row_smem));              \
         k<<<row_grid, GT_THREADS, row_smem, st>>>(src, mid, w, total_rows, rlen / 2, row_shift, rnch, in_pitch, rwl); \
     }
@@ -479,7 +575,7 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
 #undef ROW_GO2
 #define COL_GO(TCC)                                                                                                  \
     {                                                                                                                \
-        auto k = col_f32x2_kernel<Mid, T, Q15F, TCC>;                                                                \
+        auto k = cnch >= RING_MIN_CHUNKS ? col_f32x2_kernel<Mid, T, Q15F, TCC, true> : col_f32x2_kernel<Mid, T, Q15F, TCC, false>; \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem));              \
         k<<<col_grid, GT_THREADS, col_smem, st>>>((const Mid *)mid, dst, row_sub, h, tiles_y, clen / 2, cnch, zero_first_row, cwl); \
     }
