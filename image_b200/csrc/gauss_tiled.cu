@@ -469,6 +469,33 @@ col_f32x2_kernel(const Mid *__restrict__ mid, Out *__restrict__ dst, uint32_t ro
             asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(m + (size_t)y * row_sub + s0 + v * 4) : "memory");
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
+    } else if (sizeof(Mid) == 1 && (row_sub % 4 == 0) && (s0 + COL_TW <= row_sub) && ((reinterpret_cast<uintptr_t>(m) & 3) == 0)) {
+        // u8 intermediate (Q0.15 engine): a 32-bit word = four subpixels -> four floats through the
+        // 2^23 trick, stored as one 16-byte vector; four words in flight per thread
+        constexpr int WPR = COL_TW / 4;  // words per staged row
+        const int total = sr * WPR;
+        for (int i0 = tid; i0 < total; i0 += 4 * GT_THREADS) {
+            uint32_t wv[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = i0 + k * GT_THREADS;
+                const int r = i / WPR, v = i - r * WPR;
+                const int y = min(max(y0 - half + r, 0), (int)H - 1);
+                wv[k] = i < total ? __ldg(reinterpret_cast<const uint32_t *>(m + (size_t)y * row_sub + s0) + v) : 0u;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int i = i0 + k * GT_THREADS;
+                if (i < total) {
+                    float4 f;
+                    f.x = __uint_as_float(__byte_perm(wv[k], 0x4B000000u, 0x7540)) - 8388608.0f;
+                    f.y = __uint_as_float(__byte_perm(wv[k], 0x4B000000u, 0x7541)) - 8388608.0f;
+                    f.z = __uint_as_float(__byte_perm(wv[k], 0x4B000000u, 0x7542)) - 8388608.0f;
+                    f.w = __uint_as_float(__byte_perm(wv[k], 0x4B000000u, 0x7543)) - 8388608.0f;
+                    *reinterpret_cast<float4 *>(s + i * 4) = f;   // i * 4 = r * COL_TW + v * 4
+                }
+            }
+        }
     } else {
         const int c = tid % COL_TW;
         const uint32_t col = min(s0 + c, row_sub - 1);
