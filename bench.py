@@ -127,6 +127,10 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # one process per GPU: stay on the CPUs (and so the NUMA node) next to this GPU before any pinned
+    # host memory is allocated -- the e2e leg is PCIe / host-memory bound
+    from image_b200.hostutil import bind_cpu_affinity
+    cpus = bind_cpu_affinity(local)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -215,6 +219,7 @@ def run_b200(args):
                 "d2h_bytes_per_step": BATCH * W4K * H4K * 3},
         "gpu_launches": args.steps * GAUSS_LAUNCHES,
         "clocks": clk.summary(),
+        "host": {"cpu_affinity": (f"{len(cpus)} CPUs local to the GPU (NVML)" if cpus else "unbound")},
     }
 
     # ---- extras: the other hot-path families at their BASELINE shapes (rank 0 numbers, per GPU) ----
