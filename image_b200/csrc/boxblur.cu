@@ -207,16 +207,17 @@ __device__ __forceinline__ void copy_row_phased(const T *from, T *to, int n, int
 
 template <typename T, int C>
 __global__ void __launch_bounds__(THREADS)
-box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t total_rows, int in_pitch, int out_pitch) {
+box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t total_rows, int in_pitch, int out_pitch, int xt,
+             int xc) {
     typedef typename Box<T>::sum_t S;
     extern __shared__ __align__(16) unsigned char smem[];
     T *s_in = reinterpret_cast<T *>(smem);                              // [H_ROWS][in_pitch]   (pitch in elements; odd number of words)
     T *s_out = reinterpret_cast<T *>(smem) + (size_t)H_ROWS * in_pitch;  // [H_ROWS][out_pitch]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int x0 = blockIdx.x * H_XT;
+    const int x0 = blockIdx.x * xt;   // xt = output pixels per CTA tile, xc = pixels per warp chunk (host's choice)
     const size_t row0 = (size_t)blockIdx.y * H_ROWS;
     const int r = (int)g.r, W = (int)g.w;
-    const int tw = min(H_XT, W - x0);
+    const int tw = min(xt, W - x0);
     const int sp = tw + 2 * r;  // staged pixels: x0 - r .. x0 + tw - 1 + r, clamped
     const size_t g_pitch = (size_t)W * C;
     const bool interior = x0 - r >= 0 && x0 + tw + r <= W;
@@ -246,13 +247,13 @@ box_h_kernel(const T *__restrict__ src, T *__restrict__ dst, BoxGeom g, size_t t
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
-    const int chunks = (tw + H_XC - 1) / H_XC;
+    const int chunks = (tw + xc - 1) / xc;
     const size_t my_row = min(row0 + lane, total_rows - 1);
     const T *in_row = s_in + (size_t)lane * in_pitch + in_phase(my_row);
     T *out_row = s_out + (size_t)lane * out_pitch + out_phase(my_row);
     for (int item = warp; item < chunks * C; item += THREADS / 32) {
         const int ck = item / C, c = item - ck * C;
-        const int xa = ck * H_XC, xb = min(xa + H_XC, tw);  // outputs [xa, xb) of this tile
+        const int xa = ck * xc, xb = min(xa + xc, tw);  // outputs [xa, xb) of this tile
         const T *in = in_row + c;                            // staged pixel j <-> source pixel x0 - r + j
         T *out = out_row + c;
         S sum = (S)0;
@@ -321,11 +322,19 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
             if (rc == 1) { cur = (const T *)dst; continue; }
         }
         {
-            // one staged element past the last window keeps the sliding update branch-free
-            const int in_pitch = staged_pitch((H_XT + 2 * (int)g.r + 1) * C, sizeof(T));
-            const int out_pitch = staged_pitch(H_XT * C, sizeof(T));
-            const size_t smem = (size_t)H_ROWS * (in_pitch + out_pitch) * sizeof(T);
-            const dim3 grid((w + H_XT - 1) / H_XT, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
+            // one staged element past the last window keeps the sliding update branch-free.  Tile width:
+            // the widest of 256 / 128 / 64 / 32 pixels whose staged rows leave room for two CTAs per SM
+            // (f32 x 4 channels at 256 pixels would not fit at all); 32-pixel chunks keep all 8 warps busy
+            int xt = H_XT, in_pitch = 0, out_pitch = 0;
+            size_t smem = 0;
+            for (;; xt /= 2) {
+                in_pitch = staged_pitch((xt + 2 * (int)g.r + 1) * C, sizeof(T));
+                out_pitch = staged_pitch(xt * C, sizeof(T));
+                smem = (size_t)H_ROWS * (in_pitch + out_pitch) * sizeof(T);
+                if (smem <= 100 * 1024 || xt <= 32) break;
+            }
+            const int xc = std::max(8, std::min(32, xt * C / 8));
+            const dim3 grid((w + xt - 1) / xt, (unsigned)((total_rows + H_ROWS - 1) / H_ROWS));
             if (smem > ctx->smem_optin) {
                 const size_t total = total_rows * w * C;
                 const unsigned gd = (unsigned)std::min<size_t>((total + THREADS - 1) / THREADS, (size_t)ctx->sm_count * 32);
@@ -335,7 +344,7 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
     {                                                                                                       \
         auto k = box_h_kernel<T, CC>;                                                                       \
         B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));         \
-        k<<<grid, THREADS, smem, st>>>(cur, (T *)tmp, g, total_rows, in_pitch, out_pitch);                  \
+        k<<<grid, THREADS, smem, st>>>(cur, (T *)tmp, g, total_rows, in_pitch, out_pitch, xt, xc);          \
     }
             switch (C) {
                 case 1: H_GO(1) break;
