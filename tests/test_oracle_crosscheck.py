@@ -108,3 +108,62 @@ def test_oracle_weight_tables_match_independent_numpy(name):
             for i, (l, ws) in enumerate(mine):
                 assert (left[i], cnt[i]) == (l, len(ws)), (name, axis, src, dst, i)
                 assert np.array_equal(w[i, :len(ws)], np.array(ws, F)), (name, axis, src, dst, i)
+
+
+# ---- the separable convolution engine (src/imageops/filter_1d.rs) ----------
+# The 1-D kernels come from the oracle (they need expf / powf); what is rebuilt here is everything
+# after them: Q0.15 transform, zero-end stripping, replicate padding, the paired summation order of
+# the row and column passes, the intermediate of the pixel type, and the store rules.
+def _strip(k):
+    k = list(k)
+    while len(k) > 2 and k[0] == 0 and k[-1] == 0:
+        k = k[1:-1]
+    return k
+
+
+def _pass(a, k, axis, q15, maxv):
+    """a: (h, w, c) array of f32 or uint64 values; symmetric pass along `axis` with clamp-to-edge"""
+    n = a.shape[axis]
+    half = len(k) // 2
+    idx = np.arange(n)
+    take = lambda off: np.take(a, np.clip(idx + off, 0, n - 1), axis=axis)
+    if q15:
+        acc = take(0) * np.uint64(k[half])
+        for i in range(half):
+            acc = acc + (take(-(half - i)) + take(half - i)) * np.uint64(k[i])
+        return np.minimum((acc + np.uint64(16384)) >> np.uint64(15), np.uint64(maxv))
+    acc = take(0) * F(k[half])
+    for i in range(half):
+        acc = acc + (take(-(half - i)) + take(half - i)) * F(k[i])   # pair first, then multiply, then add: all f32
+    return acc
+
+
+def blur(img, kx, ky, path):
+    q15 = path == "dyn" and img.dtype != np.float32
+    if q15:
+        maxv = np.iinfo(img.dtype).max
+        tr = lambda k: _strip([int(min(max(F(v) * F(32768.0), F(0.0)), F(32767.0))) for v in k])
+        mid = _pass(img.astype(np.uint64), tr(kx), 1, True, maxv)
+        return _pass(mid, tr(ky), 0, True, maxv).astype(img.dtype)
+    out = _pass(_pass(img.astype(F), _strip(kx), 1, False, 0), _strip(ky), 0, False, 0)
+    if img.dtype == np.float32:
+        return out
+    maxv = np.iinfo(img.dtype).max
+    v = out + F(0.5)
+    return np.where(v >= maxv + 1, maxv, np.where(v > 0, np.trunc(np.minimum(v, F(maxv + 1))), 0)).astype(img.dtype)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("path", ["generic", "dyn"])
+def test_oracle_gaussian_engine_matches_independent_numpy(dtype, path):
+    rng = np.random.default_rng(23)
+    for (h, w, c) in ((9, 14, 3), (20, 7, 1), (12, 12, 4)):
+        img = rng.random((h, w, c), dtype=np.float32) if dtype == np.float32 else \
+            rng.integers(0, np.iinfo(dtype).max + 1, (h, w, c), dtype=dtype)
+        for p in (o.gauss_params_from_sigma(1.0), o.gauss_params_from_radius(3.0), o.gauss_params_from_sigma(2.6),
+                  o.gauss_params_from_anisotropic(9.0, 3.0), o.gauss_params_from_sigma(10.0)):
+            kx = o.gaussian_kernel_1d(p.x_kernel_size, p.x_sigma)
+            ky = o.gaussian_kernel_1d(p.y_kernel_size, p.y_sigma)
+            want = blur(img, kx, ky, path)
+            got = o.gaussian_blur(img, p, path)
+            assert np.array_equal(got, want), (dtype, path, (h, w, c), p)
