@@ -8,8 +8,10 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 namespace b200 {
 
@@ -95,49 +97,102 @@ DeviceCtx *current_ctx() {
     return &(g_ctx[dev] = c);
 }
 
-// ---- scratch pool: one buffer per (device, stream, slot), grown on demand -----------
-struct ScratchBuf { void *p = nullptr; size_t bytes = 0; };
+// ---- scratch pool: buffers per (device, stream, slot), grown on demand -------------------
+// A buffer is LEASED to the host thread that asked for it until that thread's entry point returns
+// (ScratchScope), so another host thread working on the same (device, stream, slot) can neither free
+// nor share it between the first thread's scratch() and its launches: it gets a buffer of its own.
+// Between leases, re-use is ordered by the stream the key names.  Growth is stream-ordered too
+// (cudaFreeAsync / cudaMallocAsync on that stream): a `_dev` call never synchronises the device.
+struct ScratchBuf { void *p = nullptr; size_t bytes = 0; bool leased = false; };
+using ScratchKey = std::tuple<int, cudaStream_t, int>;
 static std::mutex g_scr_mu;
-static std::map<std::tuple<int, cudaStream_t, int>, ScratchBuf> g_scr;
+static std::map<ScratchKey, std::vector<ScratchBuf>> g_scr;
 static thread_local cudaStream_t g_scratch_stream = nullptr;
+static thread_local std::vector<std::pair<ScratchKey, void *>> g_leases;
 
 void set_scratch_stream(cudaStream_t st) { g_scratch_stream = st; }
+
+void release_scratch_leases() {
+    if (g_leases.empty()) return;
+    std::lock_guard<std::mutex> lk(g_scr_mu);
+    for (auto &l : g_leases) {
+        auto it = g_scr.find(l.first);
+        if (it == g_scr.end()) continue;
+        for (ScratchBuf &b : it->second)
+            if (b.p == l.second) b.leased = false;
+    }
+    g_leases.clear();
+}
 
 int scratch(ScratchSlot slot, size_t bytes, void **out) {
     int dev;
     B200_CUDA(cudaGetDevice(&dev));
+    const cudaStream_t st = g_scratch_stream;
+    const ScratchKey key = std::make_tuple(dev, st, (int)slot);
     std::lock_guard<std::mutex> lk(g_scr_mu);
-    ScratchBuf &b = g_scr[std::make_tuple(dev, g_scratch_stream, (int)slot)];
-    if (b.bytes < bytes) {
-        if (b.p) cudaFree(b.p);  // synchronises: queued kernels that use it have finished
-        b.p = nullptr; b.bytes = 0;
+    for (auto &l : g_leases)  // asked twice within one call: the same buffer if it is large enough
+        if (l.first == key)
+            for (ScratchBuf &b : g_scr[key])
+                if (b.p == l.second && b.bytes >= bytes) { *out = b.p; return B200IMG_OK; }
+    std::vector<ScratchBuf> &bufs = g_scr[key];
+    ScratchBuf *pick = nullptr;
+    for (ScratchBuf &b : bufs)
+        if (!b.leased && b.bytes >= bytes) { pick = &b; break; }
+    if (!pick) {
+        for (ScratchBuf &b : bufs)
+            if (!b.leased) { pick = &b; break; }  // too small: replaced below
+        if (!pick) { bufs.emplace_back(); pick = &bufs.back(); }
+        if (pick->p) cudaFreeAsync(pick->p, st);  // after the work already queued on `st` that uses it
+        pick->p = nullptr; pick->bytes = 0;
         const size_t want = (bytes + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
-        cudaError_t e = cudaMalloc(&b.p, want);
+        cudaError_t e = cudaMallocAsync(&pick->p, want, st);
         if (e != cudaSuccess) {
-            b.p = nullptr;
+            pick->p = nullptr;
             cudaGetLastError();
             return fail(B200IMG_ERR_OOM, "cannot allocate %zu bytes of device scratch", want);
         }
-        b.bytes = want;
+        pick->bytes = want;
     }
-    *out = b.p;
+    pick->leased = true;
+    g_leases.emplace_back(key, pick->p);
+    *out = pick->p;
     return B200IMG_OK;
 }
 
-static void release_scratch(int dev) {
+// Every entry point that may take scratch opens one of these first.
+struct ScratchScope {
+    explicit ScratchScope(cudaStream_t st) { release_scratch_leases(); set_scratch_stream(st); }
+    ~ScratchScope() { release_scratch_leases(); }
+};
+
+static void release_scratch(int dev) {  // caller has synchronised the device
     std::lock_guard<std::mutex> lk(g_scr_mu);
     for (auto it = g_scr.begin(); it != g_scr.end();) {
-        if (std::get<0>(it->first) == dev) { cudaFree(it->second.p); it = g_scr.erase(it); }
-        else ++it;
+        if (std::get<0>(it->first) == dev) {
+            for (ScratchBuf &b : it->second) cudaFree(b.p);
+            it = g_scr.erase(it);
+        } else ++it;
     }
 }
 
-static std::mutex g_host_api_mu;  // host-pointer entry points share the stream-0 scratch
+// Host-pointer entry points share the stream-0 scratch and the staging pipe of their device: one
+// call at a time per DEVICE (not per process -- one process can feed every GPU of the box at once).
+static std::mutex g_host_mu_map_mu;
+static std::map<int, std::unique_ptr<std::mutex>> g_host_mu;
+static std::mutex &host_mutex_of_current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_host_mu_map_mu);
+    auto &m = g_host_mu[dev];
+    if (!m) m.reset(new std::mutex);
+    return *m;
+}
 
 // RAII: host-pointer call = lock, device buffers, copy in ... copy out, sync
 struct HostCall {
     std::lock_guard<std::mutex> lk;
-    HostCall() : lk(g_host_api_mu) { set_scratch_stream(nullptr); }
+    ScratchScope scope;
+    HostCall() : lk(host_mutex_of_current_device()), scope(nullptr) {}
     int in(const void *h, size_t bytes, void **d) {
         int rc = scratch(SCRATCH_IO_SRC, bytes ? bytes : 1, d);
         if (rc) return rc;
@@ -150,6 +205,8 @@ struct HostCall {
         B200_CUDA(cudaStreamSynchronize(0));
         return B200IMG_OK;
     }
+    // The caller's buffers must be quiescent when an entry point returns, also when it fails midway.
+    ~HostCall() { cudaStreamSynchronize(0); }
 };
 
 // ---- host-resident batches: H2D, kernels and D2H of consecutive images overlap on three streams ----
@@ -161,12 +218,39 @@ struct HostPipe {
     size_t src_bytes = 0, dst_bytes = 0;
     bool ready = false;
 };
-static std::map<int, HostPipe> g_pipes;  // guarded by g_host_api_mu
+static std::mutex g_pipes_mu;            // guards the map; a pipe itself is used under its device's host mutex
+static std::map<int, HostPipe> g_pipes;  // std::map: references stay valid across inserts
+
+static void pipe_free_buffers(HostPipe &p) {
+    for (int i = 0; i < HostPipe::SLOTS; ++i) {
+        cudaFree(p.src[i]); cudaFree(p.dst[i]);
+        p.src[i] = p.dst[i] = nullptr;
+    }
+    p.src_bytes = p.dst_bytes = 0;
+}
+
+static void release_pipe(int dev) {  // caller holds the device's host mutex and has synchronised the device
+    std::lock_guard<std::mutex> lk(g_pipes_mu);
+    auto it = g_pipes.find(dev);
+    if (it == g_pipes.end()) return;
+    HostPipe &p = it->second;
+    pipe_free_buffers(p);
+    if (p.ready) {
+        for (int i = 0; i < HostPipe::SLOTS; ++i) { cudaEventDestroy(p.e_in[i]); cudaEventDestroy(p.e_run[i]); cudaEventDestroy(p.e_out[i]); }
+        cudaStreamDestroy(p.h2d); cudaStreamDestroy(p.exec); cudaStreamDestroy(p.d2h);
+    }
+    g_pipes.erase(it);
+}
 
 static int pipe_get(size_t sb, size_t db, HostPipe **out) {
     int dev;
     B200_CUDA(cudaGetDevice(&dev));
-    HostPipe &p = g_pipes[dev];
+    HostPipe *pp;
+    {
+        std::lock_guard<std::mutex> lk(g_pipes_mu);
+        pp = &g_pipes[dev];
+    }
+    HostPipe &p = *pp;
     if (!p.ready) {
         B200_CUDA(cudaStreamCreateWithFlags(&p.h2d, cudaStreamNonBlocking));
         B200_CUDA(cudaStreamCreateWithFlags(&p.exec, cudaStreamNonBlocking));
@@ -179,15 +263,12 @@ static int pipe_get(size_t sb, size_t db, HostPipe **out) {
         p.ready = true;
     }
     if (p.src_bytes < sb || p.dst_bytes < db) {
-        B200_CUDA(cudaDeviceSynchronize());
-        for (int i = 0; i < HostPipe::SLOTS; ++i) {
-            cudaFree(p.src[i]); cudaFree(p.dst[i]);
-            p.src[i] = p.dst[i] = nullptr;
-        }
-        p.src_bytes = p.dst_bytes = 0;
+        // the pipe is idle here: every pipe_run drains its streams before it returns
+        pipe_free_buffers(p);
         for (int i = 0; i < HostPipe::SLOTS; ++i) {
             if (cudaMalloc(&p.src[i], sb) != cudaSuccess || cudaMalloc(&p.dst[i], db) != cudaSuccess) {
                 cudaGetLastError();
+                pipe_free_buffers(p);
                 return fail(B200IMG_ERR_OOM, "cannot allocate the host-batch staging buffers (%zu + %zu bytes x %d)", sb, db, HostPipe::SLOTS);
             }
         }
@@ -199,12 +280,8 @@ static int pipe_get(size_t sb, size_t db, HostPipe **out) {
 
 // op(d_src, d_dst, stream) enqueues the device work for one image.
 template <typename Op>
-static int pipe_run(const void *hsrc, size_t sb, void *hdst, size_t db, uint32_t n, Op op) {
-    std::lock_guard<std::mutex> lk(g_host_api_mu);
-    HostPipe *p;
-    int rc = pipe_get(sb, db, &p);
-    if (rc) return rc;
-    set_scratch_stream(p->exec);
+static int pipe_enqueue(HostPipe *p, const void *hsrc, size_t sb, void *hdst, size_t db, uint32_t n, Op op) {
+    int rc;
     for (uint32_t i = 0; i < n; ++i) {
         const int s = (int)(i % HostPipe::SLOTS);
         if (i >= (uint32_t)HostPipe::SLOTS) {
@@ -220,7 +297,24 @@ static int pipe_run(const void *hsrc, size_t sb, void *hdst, size_t db, uint32_t
         B200_CUDA(cudaMemcpyAsync((char *)hdst + (size_t)i * db, p->dst[s], db, cudaMemcpyDeviceToHost, p->d2h));
         B200_CUDA(cudaEventRecord(p->e_out[s], p->d2h));
     }
-    B200_CUDA(cudaStreamSynchronize(p->d2h));
+    return B200IMG_OK;
+}
+
+template <typename Op>
+static int pipe_run(const void *hsrc, size_t sb, void *hdst, size_t db, uint32_t n, Op op) {
+    std::lock_guard<std::mutex> lk(host_mutex_of_current_device());
+    HostPipe *p;
+    int rc = pipe_get(sb, db, &p);
+    if (rc) return rc;
+    ScratchScope scope(p->exec);
+    rc = pipe_enqueue(p, hsrc, sb, hdst, db, n, op);
+    // Drain all three streams whatever happened: copies queued for earlier images still read `hsrc` and
+    // write `hdst`, and the caller may free or reuse both as soon as this call has returned.
+    const cudaError_t e1 = cudaStreamSynchronize(p->h2d), e2 = cudaStreamSynchronize(p->exec), e3 = cudaStreamSynchronize(p->d2h);
+    if (rc) return rc;
+    if (e1 != cudaSuccess) return cuda_fail(e1, "host batch: upload stream");
+    if (e2 != cudaSuccess) return cuda_fail(e2, "host batch: kernel stream");
+    if (e3 != cudaSuccess) return cuda_fail(e3, "host batch: download stream");
     return B200IMG_OK;
 }
 
@@ -254,7 +348,6 @@ static int resize_front(const void *src, size_t src_stride, uint32_t w, uint32_t
         B200_CUDA(cudaMemcpy2DAsync(dst, dst_stride, src, src_stride, sb, n, cudaMemcpyDeviceToDevice, st));
         return B200IMG_OK;
     }
-    set_scratch_stream(st);
     return resize_launch(src, src_stride, 0, h, w, h, C, dtype, dst, dst_stride, 0, nh, nw, nh, n, filter, acc_init, flags, st);
 }
 
@@ -287,8 +380,11 @@ int b200img_pinned_free(void *p) {
 int b200img_release_caches(void) {
     int dev;
     B200_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(host_mutex_of_current_device());  // no host-pointer call is using the pipe
+    release_scratch_leases();
     B200_CUDA(cudaDeviceSynchronize());
     release_scratch(dev);
+    release_pipe(dev);
     resize_release_tables(dev);
     return B200IMG_OK;
 }
@@ -355,12 +451,14 @@ int b200img_boxes_for_gauss(float sigma, uint32_t out[3]) {
 // ---- resampler ----------------------------------------------------------------
 int b200img_resize_dev(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t nw, uint32_t nh,
                        int filter, float acc_init, int flags, void *stream) {
+    ScratchScope scope((cudaStream_t)stream);
     return resize_front(src, 0, w, h, C, dtype, dst, 0, nw, nh, 1, filter, acc_init, flags, (cudaStream_t)stream);
 }
 
 int b200img_resize_batch_dev(const void *src, size_t src_stride, uint32_t w, uint32_t h, int C, int dtype, void *dst,
                              size_t dst_stride, uint32_t nw, uint32_t nh, uint32_t n, int filter, float acc_init,
                              int flags, void *stream) {
+    ScratchScope scope((cudaStream_t)stream);
     return resize_front(src, src_stride, w, h, C, dtype, dst, dst_stride, nw, nh, n, filter, acc_init, flags, (cudaStream_t)stream);
 }
 
@@ -401,7 +499,16 @@ int b200img_resize_band_dev(const void *src_band, uint32_t src_row0, uint32_t sr
     if (dst_row0 + (uint64_t)dst_rows > nh || src_row0 + (uint64_t)src_rows > h)
         return fail(B200IMG_ERR_BAD_ARG, "resize_band: band outside the image");
     if (!src_band || !dst_band) return fail(B200IMG_ERR_BAD_ARG, "resize_band: null buffer");
-    set_scratch_stream((cudaStream_t)stream);
+    if (filter_support(filter) < 0) return fail(B200IMG_ERR_BAD_ARG, "resize_band: unknown filter %d", filter);
+    if (nw == w && nh == h) {  // same dimensions: imageops::resize copies (sample.rs:987-991), so does every band of it
+        if (dst_row0 < src_row0 || dst_row0 + (uint64_t)dst_rows > src_row0 + (uint64_t)src_rows)
+            return fail(B200IMG_ERR_BAD_ARG, "resize band: source band does not cover the rows the destination band copies");
+        const size_t row_bytes = sb / h;
+        B200_CUDA(cudaMemcpyAsync(dst_band, (const char *)src_band + (size_t)(dst_row0 - src_row0) * row_bytes,
+                                  (size_t)dst_rows * row_bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+        return B200IMG_OK;
+    }
+    ScratchScope scope((cudaStream_t)stream);
     return resize_launch(src_band, 0, src_row0, src_rows, w, h, C, dtype, dst_band, 0, dst_row0, dst_rows, nw, nh, 1,
                          filter, acc_init, flags, (cudaStream_t)stream);
 }
@@ -424,7 +531,7 @@ int b200img_gaussian_blur_batch_dev(const void *src, uint32_t w, uint32_t h, int
     if ((rc = gauss_check(p, path))) return rc;
     if (bytes == 0 || n == 0) return B200IMG_OK;
     if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur: null buffer");
-    set_scratch_stream((cudaStream_t)stream);
+    ScratchScope scope((cudaStream_t)stream);
     return gaussian_blur_launch(src, w, h, C, dtype, dst, n, p, path, flags, (cudaStream_t)stream);
 }
 
@@ -495,7 +602,7 @@ int b200img_fast_blur_batch_dev(const void *src, uint32_t w, uint32_t h, int C, 
     if (rc) return rc;
     if (bytes == 0 || n == 0) return B200IMG_OK;  // empty image: clone (fast_blur.rs:117-119)
     if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "fast_blur: null buffer");
-    set_scratch_stream((cudaStream_t)stream);
+    ScratchScope scope((cudaStream_t)stream);
     return fast_blur_launch(src, w, h, C, dtype, dst, n, sigma, (cudaStream_t)stream);
 }
 
@@ -590,7 +697,7 @@ int b200img_unsharpen_dev(const void *src, uint32_t w, uint32_t h, int C, int dt
     if (gauss_params_from_sigma(sigma, &p)) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: sigma must be non-negative and finite");
     if (bytes == 0) return B200IMG_OK;
     if (!src || !dst) return fail(B200IMG_ERR_BAD_ARG, "unsharpen: null buffer");
-    set_scratch_stream((cudaStream_t)stream);
+    ScratchScope scope((cudaStream_t)stream);
     return unsharpen_launch(src, w, h, C, dtype, dst, 1, sigma, threshold, flags, (cudaStream_t)stream);
 }
 
@@ -694,7 +801,7 @@ int b200img_has_constant_alpha_dev(const void *src, uint32_t w, uint32_t h, int 
     *result = 1;
     if (bytes == 0 || (C != 2 && C != 4)) return B200IMG_OK;  // resize.rs:155-171: no alpha channel / empty image
     if (!src) return fail(B200IMG_ERR_BAD_ARG, "has_constant_alpha: null buffer");
-    set_scratch_stream((cudaStream_t)stream);
+    ScratchScope scope((cudaStream_t)stream);
     return constant_alpha_on(src, (size_t)w * h, C, dtype, result, (cudaStream_t)stream);
 }
 

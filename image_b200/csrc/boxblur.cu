@@ -378,6 +378,9 @@ int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, 
     for (int i = 0; i < 3; ++i) {
         if (radii[i] >= (1u << 23))  // beyond here the reference's u8 path switches accumulators (fast_blur.rs:238-247)
             return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur: box radius %u is beyond the supported range", radii[i]);
+        // u16 running sums are u32 here (exact; the reference's are f32): they wrap once ks * 65535 >= 2^32
+        if (dtype == B200IMG_U16 && 2ull * radii[i] + 1 > 65537ull)
+            return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur: box radius %u overflows the 32-bit sums of 16-bit images", radii[i]);
     }
     size_t bytes;
     if (!checked_mul((size_t)w * h, (size_t)C, dtype_size(dtype), n_images, &bytes))
@@ -445,7 +448,8 @@ extern "C" int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint
     uint32_t radii[3];
     boxes_for_gauss(sigma, radii);
     for (int i = 0; i < 3; ++i)
-        if (radii[i] >= (1u << 23)) return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur_noalloc: box radius %u is beyond the supported range", radii[i]);
+        if (radii[i] >= (1u << 23) || (dtype == B200IMG_U16 && 2ull * radii[i] + 1 > 65537ull))
+            return fail(B200IMG_ERR_UNSUPPORTED, "fast_blur_noalloc: box radius %u is beyond the supported range", radii[i]);
 
     int dev;
     B200_CUDA(cudaGetDevice(&dev));

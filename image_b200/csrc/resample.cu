@@ -18,6 +18,7 @@
 #include "packed.cuh"
 
 #include <list>
+#include <memory>
 #include <mutex>
 #include <tuple>
 
@@ -323,52 +324,69 @@ resize_kernel(const ResizeArgs a) {
 }
 
 // ---- device-side weight tables, cached per (device, filter, lengths, axis) --------
+// Tables are handed out as shared_ptr: a launch keeps its tables alive until it has been enqueued,
+// whatever other host threads do to the cache meanwhile; the device memory goes when the last
+// holder lets go (cudaFree waits for queued kernels that still read it).
 struct DevTable {
-    int device, filter, axis;
-    uint32_t src_len, dst_len;
+    int device = -1, filter = -1, axis = -1;
+    uint32_t src_len = 0, dst_len = 0;
     AxisTable host;  // left/count kept on the host for tile planning
     int32_t *d_left = nullptr, *d_count = nullptr;
     float *d_w = nullptr;
+    DevTable() = default;
+    DevTable(const DevTable &) = delete;
+    DevTable &operator=(const DevTable &) = delete;
+    ~DevTable() {
+        if (!d_left && !d_count && !d_w) return;
+        int cur = -1;
+        cudaGetDevice(&cur);
+        if (cur != device) cudaSetDevice(device);
+        cudaFree(d_left); cudaFree(d_count); cudaFree(d_w);
+        if (cur != device && cur >= 0) cudaSetDevice(cur);
+    }
 };
+using TablePtr = std::shared_ptr<const DevTable>;
 std::mutex g_tab_mu;
-std::list<DevTable> g_tabs;  // most recently used first
-constexpr size_t MAX_TABLES = 32;
+std::list<std::shared_ptr<DevTable>> g_tabs;  // most recently used first; LRU per device
+constexpr size_t MAX_TABLES = 32;             // per device
 
-void free_table(DevTable &t) {
-    cudaFree(t.d_left); cudaFree(t.d_count); cudaFree(t.d_w);
-}
-
-int get_table(int device, int filter, uint32_t src_len, uint32_t dst_len, int axis, const DevTable **out) {
-    std::lock_guard<std::mutex> lk(g_tab_mu);
-    for (auto it = g_tabs.begin(); it != g_tabs.end(); ++it) {
-        if (it->device == device && it->filter == filter && it->axis == axis && it->src_len == src_len && it->dst_len == dst_len) {
-            g_tabs.splice(g_tabs.begin(), g_tabs, it);
-            *out = &g_tabs.front();
-            return B200IMG_OK;
+int get_table(int device, int filter, uint32_t src_len, uint32_t dst_len, int axis, TablePtr *out) {
+    {
+        std::lock_guard<std::mutex> lk(g_tab_mu);
+        for (auto it = g_tabs.begin(); it != g_tabs.end(); ++it) {
+            const DevTable &t = **it;
+            if (t.device == device && t.filter == filter && t.axis == axis && t.src_len == src_len && t.dst_len == dst_len) {
+                g_tabs.splice(g_tabs.begin(), g_tabs, it);
+                *out = g_tabs.front();
+                return B200IMG_OK;
+            }
         }
     }
-    DevTable t;
-    t.device = device; t.filter = filter; t.axis = axis; t.src_len = src_len; t.dst_len = dst_len;
-    build_axis_table(filter, src_len, dst_len, axis, t.host);
+    // build outside the lock (host arithmetic + synchronous uploads); two threads racing on the same
+    // key both build, the second insert simply shadows the first
+    auto t = std::make_shared<DevTable>();
+    t->device = device; t->filter = filter; t->axis = axis; t->src_len = src_len; t->dst_len = dst_len;
+    build_axis_table(filter, src_len, dst_len, axis, t->host);
     const size_t n = dst_len;
-    if (cudaMalloc(&t.d_left, n * 4) != cudaSuccess || cudaMalloc(&t.d_count, n * 4) != cudaSuccess ||
-        cudaMalloc(&t.d_w, t.host.w.size() * 4) != cudaSuccess) {
+    if (cudaMalloc(&t->d_left, n * 4) != cudaSuccess || cudaMalloc(&t->d_count, n * 4) != cudaSuccess ||
+        cudaMalloc(&t->d_w, t->host.w.size() * 4) != cudaSuccess) {
         cudaGetLastError();
-        free_table(t);
         return fail(B200IMG_ERR_OOM, "resize: cannot allocate weight tables");
     }
     // synchronous copies: the table is complete before any stream can use it
-    B200_CUDA(cudaMemcpy(t.d_left, t.host.left.data(), n * 4, cudaMemcpyHostToDevice));
-    B200_CUDA(cudaMemcpy(t.d_count, t.host.count.data(), n * 4, cudaMemcpyHostToDevice));
-    B200_CUDA(cudaMemcpy(t.d_w, t.host.w.data(), t.host.w.size() * 4, cudaMemcpyHostToDevice));
-    g_tabs.push_front(std::move(t));
-    if (g_tabs.size() > MAX_TABLES) {
-        // evicting a table a queued kernel still reads would be a use-after-free
-        cudaDeviceSynchronize();
-        free_table(g_tabs.back());
-        g_tabs.pop_back();
+    B200_CUDA(cudaMemcpy(t->d_left, t->host.left.data(), n * 4, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(t->d_count, t->host.count.data(), n * 4, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(t->d_w, t->host.w.data(), t->host.w.size() * 4, cudaMemcpyHostToDevice));
+    std::shared_ptr<DevTable> evicted;
+    {
+        std::lock_guard<std::mutex> lk(g_tab_mu);
+        g_tabs.push_front(t);
+        size_t mine = 0;
+        for (auto it = g_tabs.begin(); it != g_tabs.end(); ++it)
+            if ((*it)->device == device && ++mine > MAX_TABLES) { evicted = *it; g_tabs.erase(it); break; }
     }
-    *out = &g_tabs.front();
+    evicted.reset();  // freed here (outside the lock) unless a launch in flight on another thread still holds it
+    *out = t;
     return B200IMG_OK;
 }
 
@@ -553,12 +571,11 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     if (!ctx) return B200IMG_ERR_CUDA;
     const int tsize = (int)dtype_size(dtype);
 
-    const DevTable *vt, *ht;
+    TablePtr vt, ht;  // held until this launch has been enqueued
     int rc = get_table(ctx->device, filter, h, nh, 0, &vt);
     if (rc) return rc;
     rc = get_table(ctx->device, filter, w, nw, 1, &ht);
     if (rc) return rc;
-    // copy what we need: a later get_table() may reorder the cache, entries stay valid
     const uint32_t e = dst_row0 + dst_rows - 1;
     if ((uint32_t)vt->host.left[dst_row0] < src_row0 ||
         (uint32_t)(vt->host.left[e] + vt->host.count[e]) > src_row0 + src_rows)
@@ -621,10 +638,13 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
 
 void resize_release_tables(int device) {
     resize_group_release(device);
-    std::lock_guard<std::mutex> lk(g_tab_mu);
-    for (auto it = g_tabs.begin(); it != g_tabs.end();) {
-        if (it->device == device) { free_table(*it); it = g_tabs.erase(it); }
-        else ++it;
+    std::list<std::shared_ptr<DevTable>> dropped;
+    {
+        std::lock_guard<std::mutex> lk(g_tab_mu);
+        for (auto it = g_tabs.begin(); it != g_tabs.end();) {
+            if ((*it)->device == device) { dropped.push_back(*it); it = g_tabs.erase(it); }
+            else ++it;
+        }
     }
 }
 

@@ -21,6 +21,7 @@
 #include "packed.cuh"
 
 #include <list>
+#include <memory>
 #include <mutex>
 #include <vector>
 
@@ -463,21 +464,36 @@ struct GroupTable {
     uint32_t src_len = 0, dst_len = 0;
     float2 *d_wt = nullptr;
     int2 *d_bu = nullptr;
+    GroupTable() = default;
+    GroupTable(const GroupTable &) = delete;
+    GroupTable &operator=(const GroupTable &) = delete;
+    ~GroupTable() {
+        if (!d_wt && !d_bu) return;
+        int cur = -1;
+        cudaGetDevice(&cur);
+        if (cur != device) cudaSetDevice(device);
+        cudaFree(d_wt); cudaFree(d_bu);  // waits for queued kernels that still read them
+        if (cur != device && cur >= 0) cudaSetDevice(cur);
+    }
 };
+using GroupPtr = std::shared_ptr<const GroupTable>;  // a launch holds its tables until it is enqueued
 std::mutex g_gt_mu;
-std::list<GroupTable> g_gts;  // most recently used first
-constexpr size_t MAX_GROUP_TABLES = 32;
+std::list<std::shared_ptr<GroupTable>> g_gts;  // most recently used first; LRU per device
+constexpr size_t MAX_GROUP_TABLES = 32;        // per device
 
 int get_group_table(int device, int filter, int axis, uint32_t src_len, const AxisTable &t, uint32_t dst_len, int U,
-                    const GroupTable **out) {
-    std::lock_guard<std::mutex> lk(g_gt_mu);
-    for (auto it = g_gts.begin(); it != g_gts.end(); ++it)
-        if (it->device == device && it->filter == filter && it->axis == axis && it->src_len == src_len && it->dst_len == dst_len &&
-            it->U == U) {
-            g_gts.splice(g_gts.begin(), g_gts, it);
-            *out = &g_gts.front();
-            return B200IMG_OK;
+                    GroupPtr *out) {
+    {
+        std::lock_guard<std::mutex> lk(g_gt_mu);
+        for (auto it = g_gts.begin(); it != g_gts.end(); ++it) {
+            const GroupTable &g = **it;
+            if (g.device == device && g.filter == filter && g.axis == axis && g.src_len == src_len && g.dst_len == dst_len && g.U == U) {
+                g_gts.splice(g_gts.begin(), g_gts, it);
+                *out = g_gts.front();
+                return B200IMG_OK;
+            }
         }
+    }
     const uint32_t groups = (dst_len + GR - 1) / GR;
     std::vector<float2> wt((size_t)groups * U * GR, make_float2(0.0f, 0.0f));
     std::vector<int2> bu(groups);
@@ -490,23 +506,25 @@ int get_group_table(int device, int filter, int axis, uint32_t src_len, const Ax
                 wt[((size_t)g * U + (t.left[o] + k - t.left[first])) * GR + (o - first)] = make_float2(w, w);
             }
     }
-    GroupTable gt;
-    gt.device = device; gt.filter = filter; gt.axis = axis; gt.src_len = src_len; gt.dst_len = dst_len; gt.U = U;
-    if (cudaMalloc(&gt.d_wt, wt.size() * sizeof(float2)) != cudaSuccess || cudaMalloc(&gt.d_bu, bu.size() * sizeof(int2)) != cudaSuccess) {
+    auto gt = std::make_shared<GroupTable>();
+    gt->device = device; gt->filter = filter; gt->axis = axis; gt->src_len = src_len; gt->dst_len = dst_len; gt->U = U;
+    if (cudaMalloc(&gt->d_wt, wt.size() * sizeof(float2)) != cudaSuccess || cudaMalloc(&gt->d_bu, bu.size() * sizeof(int2)) != cudaSuccess) {
         cudaGetLastError();
-        cudaFree(gt.d_wt);
         return fail(B200IMG_ERR_OOM, "resize: cannot allocate group tables");
     }
     // synchronous copies: complete before any stream can use them
-    B200_CUDA(cudaMemcpy(gt.d_wt, wt.data(), wt.size() * sizeof(float2), cudaMemcpyHostToDevice));
-    B200_CUDA(cudaMemcpy(gt.d_bu, bu.data(), bu.size() * sizeof(int2), cudaMemcpyHostToDevice));
-    g_gts.push_front(gt);
-    if (g_gts.size() > MAX_GROUP_TABLES) {
-        cudaDeviceSynchronize();  // a queued kernel may still read the evicted table
-        cudaFree(g_gts.back().d_wt); cudaFree(g_gts.back().d_bu);
-        g_gts.pop_back();
+    B200_CUDA(cudaMemcpy(gt->d_wt, wt.data(), wt.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(gt->d_bu, bu.data(), bu.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    std::shared_ptr<GroupTable> evicted;
+    {
+        std::lock_guard<std::mutex> lk(g_gt_mu);
+        g_gts.push_front(gt);
+        size_t mine = 0;
+        for (auto it = g_gts.begin(); it != g_gts.end(); ++it)
+            if ((*it)->device == device && ++mine > MAX_GROUP_TABLES) { evicted = *it; g_gts.erase(it); break; }
     }
-    *out = &g_gts.front();
+    evicted.reset();
+    *out = gt;
     return B200IMG_OK;
 }
 
@@ -534,10 +552,13 @@ int launch_gt(const GroupArgs &a, int C, size_t smem, dim3 grid, bool strict, cu
 // Returns 1 if this kernel took the job (and launched it), 0 if it does not apply (the caller
 // falls back to resize_kernel), < 0 on error.
 void resize_group_release(int device) {
-    std::lock_guard<std::mutex> lk(g_gt_mu);
-    for (auto it = g_gts.begin(); it != g_gts.end();) {
-        if (it->device == device) { cudaFree(it->d_wt); cudaFree(it->d_bu); it = g_gts.erase(it); }
-        else ++it;
+    std::list<std::shared_ptr<GroupTable>> dropped;
+    {
+        std::lock_guard<std::mutex> lk(g_gt_mu);
+        for (auto it = g_gts.begin(); it != g_gts.end();) {
+            if ((*it)->device == device) { dropped.push_back(*it); it = g_gts.erase(it); }
+            else ++it;
+        }
     }
 }
 
@@ -560,10 +581,10 @@ int resize_group_try(int filter, uint32_t h, const void *src, size_t src_img_str
     GroupPlan p;
     const size_t budget = std::min<size_t>(ctx->smem_optin, 150 * 1024);
     if (!plan_group(vt, ht, dst_row0, dst_rows, nw, C, tsize, UV, UH, budget, &p)) return 0;
-    const GroupTable *gv, *gh;
+    GroupPtr gv, gh;  // held until the launch below has been enqueued
     int rc = get_group_table(ctx->device, filter, 0, h, vt, nh, UV, &gv);
     if (rc) return rc;
-    const float2 *vwt = gv->d_wt; const int2 *vbu = gv->d_bu;   // copied: the next call may reorder the cache
+    const float2 *vwt = gv->d_wt; const int2 *vbu = gv->d_bu;
     if ((rc = get_group_table(ctx->device, filter, 1, w, ht, nw, UH, &gh))) return rc;
     const int tiles_x = (int)((nw + p.TW - 1) / p.TW), tiles_y = (int)((dst_rows + p.TH - 1) / p.TH);
     if (tiles_y > 65535 || n_images > 65535) return 0;

@@ -108,8 +108,14 @@ def _is_torch(x) -> bool:
 class _Img:
     """(pointer, w, h, c, dtype) view of a numpy array or CUDA tensor."""
 
-    def __init__(self, a):
+    def __init__(self, a, inplace: bool = False):
         self.torch = _is_torch(a)
+        if inplace:
+            # an in-place operator on a non-contiguous view would run on a temporary copy and leave
+            # the caller's image untouched without a word
+            ok = a.is_contiguous() if self.torch else (isinstance(a, np.ndarray) and a.flags.c_contiguous and a.flags.writeable)
+            if not ok:
+                raise ValueError("in-place operators need a contiguous (and, on the host, writable) image")
         if self.torch:
             import torch
             if not a.is_cuda:
@@ -308,7 +314,7 @@ def has_constant_alpha(image) -> bool:
 
 
 def _alpha_mul(name: str, image):
-    im = _Img(image)
+    im = _Img(image, inplace=True)
     lib = L.lib()
     if im.torch:
         with _on_device(im):
@@ -342,7 +348,7 @@ def convert_resize(image, dst_channels: int, dst_dtype, nwidth: int, nheight: in
 
 
 def _colorop(name: str, image, *params, out=None):
-    im = _Img(image)
+    im = _Img(image, inplace=out is image)
     if out is None:
         out = im.empty_like()
     lib = L.lib()

@@ -75,3 +75,40 @@ def test_noalloc_largest_image_and_size_limit(cuda):
     # argument errors are reported like the ordinary entry point's
     assert lib.b200img_fast_blur_noalloc_dev(big.data_ptr(), 8, 8, 5, L.U8, out.data_ptr(), 1.0, stream) == L.ERR_BAD_ARG
     assert lib.b200img_fast_blur_noalloc_dev(big.data_ptr(), 0, 0, 3, L.U8, out.data_ptr(), 1.0, stream) == 0
+
+
+def test_noalloc_agrees_with_the_oracle(cuda):
+    """Not only GPU against GPU: the reference's own arithmetic (CPU restatement) is the judge."""
+    import torch
+    import oracle
+    lib = L.lib()
+    rng = np.random.default_rng(23)
+    stream = torch.cuda.current_stream().cuda_stream
+    for (h, w, c), sigma in (((157, 203, 3), 4.0), ((64, 90, 4), 10.0)):
+        img = rng.integers(0, 256, (h, w, c), dtype=np.uint8)
+        dev = torch.from_numpy(img).to(cuda)
+        out = torch.empty_like(dev)
+        L.check(lib.b200img_fast_blur_noalloc_dev(dev.data_ptr(), w, h, c, L.U8, out.data_ptr(), sigma, stream))
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), oracle.fast_blur(img, sigma))
+
+
+def test_noalloc_really_allocates_nothing(cuda):
+    """The property the entry point exists for.  A caller whose pool owns the whole GPU sees device
+    memory in use; so after a first call (which only looks up the array's address) the free-memory
+    figure of the driver must not move across further calls."""
+    import torch
+    lib = L.lib()
+    # torch.cuda.mem_get_info is cudaMemGetInfo: the driver's figure, which counts every allocation of the
+    # process whichever copy of the runtime made it (the library links its own, statically)
+    stream = torch.cuda.current_stream().cuda_stream
+    img = torch.randint(0, 256, (1201, 1603, 4), dtype=torch.uint8, device=cuda)
+    out = torch.empty_like(img)
+    L.check(lib.b200img_fast_blur_noalloc_dev(img.data_ptr(), 1603, 1201, 4, L.U8, out.data_ptr(), 6.0, stream))
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info(cuda)
+    for sigma in (6.0, 2.0, 15.0):
+        L.check(lib.b200img_fast_blur_noalloc_dev(img.data_ptr(), 1603, 1201, 4, L.U8, out.data_ptr(), sigma, stream))
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info(cuda)
+    assert free_after == free_before, (free_before, free_after)
