@@ -29,6 +29,13 @@ class GaussParams(C.Structure):
                 f"y=({self.y_kernel_size}, {self.y_sigma}))")
 
 
+class Band(C.Structure):
+    """b200img_band: one device's share of a row-band split (include/b200img.h)."""
+    _fields_ = [("device", C.c_int), ("d_src", C.c_void_p), ("src_row0", C.c_uint32), ("src_rows", C.c_uint32),
+                ("own_row0", C.c_uint32), ("own_rows", C.c_uint32), ("d_dst", C.c_void_p),
+                ("dst_row0", C.c_uint32), ("dst_rows", C.c_uint32)]
+
+
 class B200ImgError(RuntimeError):
     def __init__(self, status: int, message: str):
         super().__init__(f"b200img status {status}: {message}")
@@ -39,6 +46,7 @@ class B200ImgError(RuntimeError):
 _vp, _u32, _i, _f, _sz = C.c_void_p, C.c_uint32, C.c_int, C.c_float, C.c_size_t
 _P = C.POINTER(GaussParams)
 _pu32 = C.POINTER(C.c_uint32)
+_B = C.POINTER(Band)
 
 # name -> (restype, argtypes); every symbol include/b200img.h declares
 SIGNATURES = {
@@ -74,6 +82,17 @@ SIGNATURES = {
     "b200img_fast_blur_batch": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f]),
     "b200img_fast_blur_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _f, _vp]),
     "b200img_fast_blur_noalloc_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _f, _vp]),
+    "b200img_plan_resize_bands": (_i, [_u32, _u32, _i, _i, _B]),
+    "b200img_plan_gaussian_blur_bands": (_i, [_u32, _P, _i, _B]),
+    "b200img_plan_fast_blur_bands": (_i, [_u32, _f, _i, _B]),
+    "b200img_exchange_ghost_rows": (_i, [_B, _i, _u32, _sz, _vp]),
+    "b200img_resize_bands": (_i, [_B, _i, _u32, _u32, _i, _i, _u32, _u32, _i, _f, _i, _vp]),
+    "b200img_gaussian_blur_bands": (_i, [_B, _i, _u32, _u32, _i, _i, _P, _i, _i, _vp]),
+    "b200img_fast_blur_bands": (_i, [_B, _i, _u32, _u32, _i, _i, _f, _vp]),
+    "b200img_gaussian_blur_band_src_rows": (_i, [_u32, _P, _u32, _u32, _pu32, _pu32]),
+    "b200img_gaussian_blur_band_dev": (_i, [_vp, _u32, _u32, _u32, _u32, _i, _i, _vp, _u32, _u32, _P, _i, _i, _vp]),
+    "b200img_fast_blur_band_src_rows": (_i, [_u32, _f, _u32, _u32, _pu32, _pu32]),
+    "b200img_fast_blur_band_dev": (_i, [_vp, _u32, _u32, _u32, _u32, _i, _i, _vp, _u32, _u32, _f, _vp]),
     "b200img_thumbnail": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i]),
     "b200img_thumbnail_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _i, _vp]),
     "b200img_thumbnail_batch_dev": (_i, [_vp, _u32, _u32, _i, _i, _vp, _u32, _u32, _u32, _i, _vp]),

@@ -27,7 +27,7 @@ int resize_band_src_rows(uint32_t h, uint32_t nh, int filter, uint32_t dst_row0,
                          uint32_t *src_row0, uint32_t *src_rows);
 void resize_release_tables(int device);
 int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
-                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st);
+                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st, bool image_top = true);
 int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      float sigma, cudaStream_t st);
 int thumbnail_check(uint32_t w, uint32_t h, int dtype, uint32_t nw, uint32_t nh);
@@ -158,12 +158,6 @@ int scratch(ScratchSlot slot, size_t bytes, void **out) {
     *out = pick->p;
     return B200IMG_OK;
 }
-
-// Every entry point that may take scratch opens one of these first.
-struct ScratchScope {
-    explicit ScratchScope(cudaStream_t st) { release_scratch_leases(); set_scratch_stream(st); }
-    ~ScratchScope() { release_scratch_leases(); }
-};
 
 static void release_scratch(int dev) {  // caller has synchronised the device
     std::lock_guard<std::mutex> lk(g_scr_mu);

@@ -33,8 +33,16 @@ DeviceCtx *current_ctx();
 // Slots are independent buffers; contents are undefined on return.
 enum ScratchSlot { SCRATCH_TABLES = 0, SCRATCH_A = 1, SCRATCH_B = 2, SCRATCH_IO_SRC = 3, SCRATCH_IO_DST = 4, SCRATCH_MID = 5, SCRATCH_FLAG = 6, SCRATCH_SLOTS = 7 };
 int scratch(ScratchSlot slot, size_t bytes, void **out);
-// Scratch is keyed by (device, stream): entry points name their stream before asking for scratch.
+// Scratch is keyed by (device, stream) and leased to the calling host thread until its entry point
+// returns: every entry point that may take scratch opens a ScratchScope first.
 void set_scratch_stream(cudaStream_t st);
+void release_scratch_leases();
+struct ScratchScope {
+    explicit ScratchScope(cudaStream_t st) { release_scratch_leases(); set_scratch_stream(st); }
+    ~ScratchScope() { release_scratch_leases(); }
+    ScratchScope(const ScratchScope &) = delete;
+    ScratchScope &operator=(const ScratchScope &) = delete;
+};
 
 inline size_t dtype_size(int dtype) { return dtype == B200IMG_U8 ? 1 : dtype == B200IMG_U16 ? 2 : 4; }
 inline bool valid_dtype(int d) { return d == B200IMG_U8 || d == B200IMG_U16 || d == B200IMG_F32; }

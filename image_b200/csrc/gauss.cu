@@ -136,8 +136,10 @@ int run(const void *src, void *dst, void *mid, const uint32_t *d_rk, const uint3
 
 }  // namespace
 
+// image_top = false: row 0 of `src` is not the image's first row (a row band of a larger image), so the
+// 1-tap ring-queue quirk, which is about the image's row 0, does not apply to it.
 int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
-                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st) {
+                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st, bool image_top) {
     DeviceCtx *ctx = current_ctx();
     if (!ctx) return B200IMG_ERR_CUDA;
     const std::vector<float> kx = gaussian_kernel_1d(p->x_kernel_size, p->x_sigma);
@@ -160,7 +162,7 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
     g.row_len = (int)rk.size(); g.col_len = (int)ck.size();
     g.row_shift = rk.size() == 1 ? 1 : 0;
     // ring-queue variant is chosen on the unscanned column length (filter_1d.rs:673)
-    g.zero_first_row = (ky.size() < 55 && ck.size() == 1) ? 1 : 0;
+    g.zero_first_row = (image_top && ky.size() < 55 && ck.size() == 1) ? 1 : 0;
 
     size_t total;
     if (!checked_mul(w, h, (size_t)C, n_images, &total)) return fail(B200IMG_ERR_DIMENSION, "gaussian_blur: size overflows");

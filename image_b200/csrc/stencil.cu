@@ -10,7 +10,7 @@
 namespace b200 {
 
 int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
-                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st);
+                         const b200img_gauss_params *p, int path, int flags, cudaStream_t st, bool image_top = true);
 
 namespace {
 

@@ -107,3 +107,65 @@ def resize_band(band_src, band: Band, w: int, h: int, nw: int, nh: int, filter: 
                   out.data_ptr(), band.dst_row0, band.dst_rows, nw, nh, int(filter), float(acc_init), flags,
                   torch.cuda.current_stream(band_src.device).cuda_stream)
     return out
+
+
+# ---- the in-library split: one host thread drives every device (csrc/multi.cu) -------------------
+def plan_bands(op: str, h: int, n_bands: int, *, nh: int = 0, filter: FilterType = FilterType.Nearest, params=None,
+               sigma: float = 0.0):
+    """(ctypes array of n_bands `_lib.Band`) row fields for an even split: op = 'resize' | 'gaussian' | 'fast_blur'."""
+    lib = L.lib()
+    arr = (L.Band * n_bands)()
+    if op == "resize":
+        _call(lib.b200img_plan_resize_bands, h, nh, int(filter), n_bands, arr)
+    elif op == "gaussian":
+        _call(lib.b200img_plan_gaussian_blur_bands, h, C.byref(params.raw), n_bands, arr)
+    elif op == "fast_blur":
+        _call(lib.b200img_plan_fast_blur_bands, h, float(sigma), n_bands, arr)
+    else:
+        raise ValueError(op)
+    return arr
+
+
+def run_bands(op: str, image, devices, *, nw: int = 0, nh: int = 0, filter: FilterType = FilterType.Nearest,
+              acc_init: float = 1.0, flags: int = L.FP_FAST, params=None, path: int = L.BLUR_GENERIC, sigma: float = 0.0,
+              ghost_fill: int = 0xAB):
+    """Runs `op` on a host image (numpy (h, w, c)) split over `devices` (CUDA ordinals, one band each; an
+    ordinal may repeat) through b200img_{resize,gaussian_blur,fast_blur}_bands.  Every device receives its
+    OWN rows only; its ghost rows start as `ghost_fill` bytes and are filled by the library.  Returns the
+    stitched result as a numpy array.  (A test / demo harness: a real caller keeps the bands resident.)"""
+    import numpy as np
+    import torch
+    lib = L.lib()
+    h, w, c = image.shape
+    n = len(devices)
+    oh = nh if op == "resize" else h
+    ow = nw if op == "resize" else w
+    bands = plan_bands(op, h, n, nh=nh, filter=filter, params=params, sigma=sigma)
+    dt = {np.dtype(np.uint8): L.U8, np.dtype(np.uint16): L.U16, np.dtype(np.float32): L.F32}[image.dtype]
+    keep = []
+    for k, d in enumerate(devices):
+        b = bands[k]
+        dev = torch.device("cuda", d)
+        src = torch.full((max(b.src_rows, 1) * w * c * image.dtype.itemsize,), ghost_fill, dtype=torch.uint8, device=dev)
+        if b.own_rows:
+            own = np.ascontiguousarray(image[b.own_row0:b.own_row0 + b.own_rows]).view(np.uint8).reshape(-1)
+            off = (b.own_row0 - b.src_row0) * w * c * image.dtype.itemsize
+            src[off:off + own.size] = torch.from_numpy(own).to(dev)
+        dst = torch.zeros((max(b.dst_rows, 1) * ow * c * image.dtype.itemsize,), dtype=torch.uint8, device=dev)
+        b.device, b.d_src, b.d_dst = d, src.data_ptr(), dst.data_ptr()
+        keep.append((src, dst))
+    for d in set(devices):
+        torch.cuda.synchronize(d)
+    if op == "resize":
+        _call(lib.b200img_resize_bands, bands, n, w, h, c, dt, nw, nh, int(filter), float(acc_init), flags, None)
+    elif op == "gaussian":
+        _call(lib.b200img_gaussian_blur_bands, bands, n, w, h, c, dt, C.byref(params.raw), path, flags, None)
+    else:
+        _call(lib.b200img_fast_blur_bands, bands, n, w, h, c, dt, float(sigma), None)
+    out = np.empty((oh, ow, c), image.dtype)
+    for k in range(n):
+        b = bands[k]
+        if b.dst_rows:
+            raw = keep[k][1].cpu().numpy()[:b.dst_rows * ow * c * image.dtype.itemsize]
+            out[b.dst_row0:b.dst_row0 + b.dst_rows] = raw.view(image.dtype).reshape(b.dst_rows, ow, c)
+    return out

@@ -222,6 +222,67 @@ int b200img_fast_blur_batch_dev(const void *d_src, uint32_t w, uint32_t h, int c
 int b200img_fast_blur_noalloc_dev(const void *d_src, uint32_t w, uint32_t h, int channels, int dtype,
                                   void *d_dst, float sigma, void *stream);
 
+/* ---- one image over several GPUs: row bands with ghost rows ------------------
+ * The path has no reduction across shards, so nothing here is a collective and NCCL is not
+ * involved: a band reads a few source rows beyond its own (the rows its vertical taps touch,
+ * src/imageops/sample.rs:494-562; taps/2 rows for the Gaussian, whose column pass clamps at the
+ * IMAGE's edges only, src/imageops/filter_1d.rs:102-130; r1+r2+r3 rows for the three composed
+ * boxes of fast_blur, src/imageops/fast_blur.rs:303-473).  Those "ghost rows" are copied once
+ * from the bands that own them (cudaMemcpyPeerAsync: NVLink where peer access exists), then every
+ * device runs the ordinary kernels on its band.  Bands are never split in x: the horizontal
+ * passes need whole rows (sample.rs:217-340).  Results are those of the whole-image call
+ * (bit-identical where that is bit-exact).
+ *
+ * A b200img_band describes one device's share.  d_src is a buffer on `device` holding source rows
+ * [src_row0, src_row0 + src_rows); of these the device OWNS [own_row0, own_row0 + own_rows), which
+ * must be valid on entry (ordered on the band's stream), and the call fills the others.  d_dst
+ * receives destination rows [dst_row0, dst_row0 + dst_rows).  The plan functions fill the six row
+ * fields for an even split over n_bands (the caller sets device, d_src, d_dst afterwards).
+ *
+ * `streams`: NULL = internal per-device streams, the call returns when every band is done; or an
+ * array of n_bands cudaStream_t (one per band, on that band's device): work is enqueued and the
+ * call returns without waiting.  One host thread drives all devices; the calling thread's current
+ * device is restored. */
+typedef struct {
+    int device;
+    void *d_src;
+    uint32_t src_row0, src_rows;
+    uint32_t own_row0, own_rows;
+    void *d_dst;
+    uint32_t dst_row0, dst_rows;
+} b200img_band;
+int b200img_plan_resize_bands(uint32_t h, uint32_t nh, int filter, int n_bands, b200img_band *bands);
+int b200img_plan_gaussian_blur_bands(uint32_t h, const b200img_gauss_params *params, int n_bands, b200img_band *bands);
+int b200img_plan_fast_blur_bands(uint32_t h, float sigma, int n_bands, b200img_band *bands);
+/* only the ghost-row copies (row_bytes = bytes of one source row) */
+int b200img_exchange_ghost_rows(const b200img_band *bands, int n_bands, uint32_t h, size_t row_bytes,
+                                void *const *streams);
+/* imageops::resize of one w x h image into nw x nh, band by band */
+int b200img_resize_bands(const b200img_band *bands, int n_bands, uint32_t w, uint32_t h, int channels, int dtype,
+                         uint32_t nw, uint32_t nh, int filter, float acc_init, int flags, void *const *streams);
+/* imageops::blur_advanced / DynamicImage::blur_advanced of one w x h image, band by band */
+int b200img_gaussian_blur_bands(const b200img_band *bands, int n_bands, uint32_t w, uint32_t h, int channels,
+                                int dtype, const b200img_gauss_params *params, int path, int flags,
+                                void *const *streams);
+/* imageops::fast_blur of one w x h image, band by band */
+int b200img_fast_blur_bands(const b200img_band *bands, int n_bands, uint32_t w, uint32_t h, int channels, int dtype,
+                            float sigma, void *const *streams);
+/* One band on the current device, ghost rows already in place (what the calls above run per
+ * device; also the building block of a one-process-per-GPU split).  d_src_band holds source rows
+ * [src_row0, src_row0 + src_rows), which must include every row the destination rows read
+ * (b200img_*_band_src_rows). */
+int b200img_gaussian_blur_band_src_rows(uint32_t h, const b200img_gauss_params *params, uint32_t dst_row0,
+                                        uint32_t dst_rows, uint32_t *src_row0, uint32_t *src_rows);
+int b200img_gaussian_blur_band_dev(const void *d_src_band, uint32_t src_row0, uint32_t src_rows, uint32_t w,
+                                   uint32_t h, int channels, int dtype, void *d_dst_band, uint32_t dst_row0,
+                                   uint32_t dst_rows, const b200img_gauss_params *params, int path, int flags,
+                                   void *stream);
+int b200img_fast_blur_band_src_rows(uint32_t h, float sigma, uint32_t dst_row0, uint32_t dst_rows,
+                                    uint32_t *src_row0, uint32_t *src_rows);
+int b200img_fast_blur_band_dev(const void *d_src_band, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h,
+                               int channels, int dtype, void *d_dst_band, uint32_t dst_row0, uint32_t dst_rows,
+                               float sigma, void *stream);
+
 /* ---- thumbnail (the first caller next to the core path) --------------------
  * imageops::thumbnail, src/imageops/sample.rs:564-886 (DynamicImage::thumbnail_exact,
  * src/images/dynimage.rs:1175).  Integer images are bit-exact, including the reference's

@@ -24,6 +24,21 @@ pub struct b200img_gauss_params {
 
 pub type Stream = *mut c_void; // cudaStream_t
 
+/// One device's share of a row-band split (`b200img_band`).
+#[repr(C)]
+#[derive(Clone, Copy, Debug)]
+pub struct b200img_band {
+    pub device: c_int,
+    pub d_src: *mut c_void,
+    pub src_row0: u32,
+    pub src_rows: u32,
+    pub own_row0: u32,
+    pub own_rows: u32,
+    pub d_dst: *mut c_void,
+    pub dst_row0: u32,
+    pub dst_rows: u32,
+}
+
 extern "C" {
     pub fn b200img_last_error() -> *const c_char;
     pub fn b200img_version() -> c_int;
@@ -80,6 +95,32 @@ extern "C" {
                                        n_images: u32, sigma: c_float, stream: Stream) -> c_int;
     pub fn b200img_fast_blur_noalloc_dev(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int,
                                          dst: *mut c_void, sigma: c_float, stream: Stream) -> c_int;
+
+    pub fn b200img_plan_resize_bands(h: u32, nh: u32, filter: c_int, n_bands: c_int, bands: *mut b200img_band) -> c_int;
+    pub fn b200img_plan_gaussian_blur_bands(h: u32, params: *const b200img_gauss_params, n_bands: c_int,
+                                            bands: *mut b200img_band) -> c_int;
+    pub fn b200img_plan_fast_blur_bands(h: u32, sigma: c_float, n_bands: c_int, bands: *mut b200img_band) -> c_int;
+    pub fn b200img_exchange_ghost_rows(bands: *const b200img_band, n_bands: c_int, h: u32, row_bytes: usize,
+                                       streams: *const Stream) -> c_int;
+    pub fn b200img_resize_bands(bands: *const b200img_band, n_bands: c_int, w: u32, h: u32, channels: c_int, dtype: c_int,
+                                nw: u32, nh: u32, filter: c_int, acc_init: c_float, flags: c_int,
+                                streams: *const Stream) -> c_int;
+    pub fn b200img_gaussian_blur_bands(bands: *const b200img_band, n_bands: c_int, w: u32, h: u32, channels: c_int,
+                                       dtype: c_int, params: *const b200img_gauss_params, path: c_int, flags: c_int,
+                                       streams: *const Stream) -> c_int;
+    pub fn b200img_fast_blur_bands(bands: *const b200img_band, n_bands: c_int, w: u32, h: u32, channels: c_int, dtype: c_int,
+                                   sigma: c_float, streams: *const Stream) -> c_int;
+    pub fn b200img_gaussian_blur_band_src_rows(h: u32, params: *const b200img_gauss_params, dst_row0: u32, dst_rows: u32,
+                                               src_row0: *mut u32, src_rows: *mut u32) -> c_int;
+    pub fn b200img_gaussian_blur_band_dev(src_band: *const c_void, src_row0: u32, src_rows: u32, w: u32, h: u32,
+                                          channels: c_int, dtype: c_int, dst_band: *mut c_void, dst_row0: u32, dst_rows: u32,
+                                          params: *const b200img_gauss_params, path: c_int, flags: c_int,
+                                          stream: Stream) -> c_int;
+    pub fn b200img_fast_blur_band_src_rows(h: u32, sigma: c_float, dst_row0: u32, dst_rows: u32, src_row0: *mut u32,
+                                           src_rows: *mut u32) -> c_int;
+    pub fn b200img_fast_blur_band_dev(src_band: *const c_void, src_row0: u32, src_rows: u32, w: u32, h: u32, channels: c_int,
+                                      dtype: c_int, dst_band: *mut c_void, dst_row0: u32, dst_rows: u32, sigma: c_float,
+                                      stream: Stream) -> c_int;
 
     pub fn b200img_thumbnail(src: *const c_void, w: u32, h: u32, channels: c_int, dtype: c_int, dst: *mut c_void,
                              nw: u32, nh: u32, flags: c_int) -> c_int;
