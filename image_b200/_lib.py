@@ -14,6 +14,7 @@ SO_PATH = os.path.join(_HERE, "lib", "libb200img.so")
 U8, U16, F32 = 0, 1, 2
 NEAREST, TRIANGLE, CATMULLROM, GAUSSIAN, LANCZOS3 = range(5)
 FP_FAST, FP_STRICT, FP_FUSED_MAC, RESIZE_UNFUSED, RESIZE_TILED, THUMBNAIL_PER_PIXEL = 0, 1, 2, 256, 512, 1024
+GAUSS_TWO_KERNELS, GAUSS_FUSED = 2048, 4096
 BLUR_GENERIC, BLUR_DYN = 0, 1
 CAST, CONVERT = 0, 1
 OK, ERR_BAD_ARG, ERR_DIMENSION, ERR_OOM, ERR_CUDA, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5

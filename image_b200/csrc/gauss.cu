@@ -28,6 +28,12 @@ int gauss_tiled_run(const T *src, T *dst, Mid *mid, uint32_t w, uint32_t h, int 
                     const uint32_t *rk, int rlen, const uint32_t *ck, int clen, int row_shift, int zero_first_row,
                     cudaStream_t st);
 
+// gauss_fused.cu: both passes in one kernel, intermediate in shared memory (1 = does not apply)
+template <typename T>
+int gauss_fused_run(const T *src, T *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t src_row0,
+                    uint32_t src_rows_buf, uint32_t dst_row0, uint32_t dst_rows, const uint32_t *rk, int rlen,
+                    const uint32_t *ck, int clen, bool q15, bool force, const DeviceCtx *ctx, cudaStream_t st);
+
 namespace {
 
 constexpr int THREADS = 256;
@@ -172,6 +178,18 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
     if (rc) return rc;
 
     const bool strict = (flags & B200IMG_FP_STRICT) != 0;
+    // One kernel for both passes (gauss_fused.cu) wherever reordering the sum is allowed and the job is one it
+    // wins on (long kernels, enough chunks per SM; B200IMG_GAUSS_FUSED skips that test); it declines (returns 1)
+    // what it does not cover.
+    if (((q15 && dtype == B200IMG_U8) || (!q15 && !strict)) && image_top && !(flags & B200IMG_GAUSS_TWO_KERNELS)) {
+        int fr;
+        const bool force = (flags & B200IMG_GAUSS_FUSED) != 0;
+        const int rl = (int)rk.size(), cl = (int)ck.size();
+        if (dtype == B200IMG_U8) fr = gauss_fused_run<uint8_t>((const uint8_t *)src, (uint8_t *)dst, w, h, C, n_images, 0, h, 0, h, rk.data(), rl, ck.data(), cl, q15, force, ctx, st);
+        else if (dtype == B200IMG_U16) fr = gauss_fused_run<uint16_t>((const uint16_t *)src, (uint16_t *)dst, w, h, C, n_images, 0, h, 0, h, rk.data(), rl, ck.data(), cl, q15, force, ctx, st);
+        else fr = gauss_fused_run<float>((const float *)src, (float *)dst, w, h, C, n_images, 0, h, 0, h, rk.data(), rl, ck.data(), cl, q15, force, ctx, st);
+        if (fr != 1) return fr;
+    }
     if ((q15 || !strict) && rk.size() <= (size_t)GT_MAX_TAPS && ck.size() <= (size_t)GT_MAX_TAPS) {
         const int rl = (int)rk.size(), cl = (int)ck.size();
 #define TILED(T, Mid, Acc)                                                                                                  \

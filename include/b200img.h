@@ -67,8 +67,9 @@ typedef enum {
  * One more difference under FAST, for f32 images only: the resampler's grouped kernel walks the
  * union of four neighbouring windows with zero weights outside each sample's own window, so a
  * NON-FINITE source sample (0 * inf = NaN) can also turn up to three destination samples next to
- * the ones whose windows contain it non-finite.  STRICT treats such samples exactly as the
- * reference does. */
+ * the ones whose windows contain it non-finite.  The Gaussian blur's FAST kernels pad their
+ * kernels with zero taps in the same way (up to 7 samples beyond the window).  STRICT treats such
+ * samples exactly as the reference does. */
 #define B200IMG_FP_FAST 0
 #define B200IMG_FP_STRICT 1
 /* multiply_accumulate of the reference fuses when it is built with +fma or for
@@ -86,6 +87,14 @@ typedef enum {
 /* thumbnail only: evaluate every output pixel on its own (the kernel that serves upscales and
  * unaligned rows) even where the column-sum kernel applies.  Same results; for tests. */
 #define B200IMG_THUMBNAIL_PER_PIXEL 1024
+
+/* Gaussian blur only: run the row pass and the column pass as two kernels with the intermediate
+ * image in device scratch, even where the single fused kernel (intermediate in shared memory)
+ * applies.  Same results; exists so that both can be tested. */
+#define B200IMG_GAUSS_TWO_KERNELS 2048
+/* ... and the opposite: use the fused kernel wherever it applies, also on jobs where the library
+ * would pick the kernel pair for speed (short kernels, small images). */
+#define B200IMG_GAUSS_FUSED 4096
 
 const char *b200img_last_error(void);
 int b200img_version(void);

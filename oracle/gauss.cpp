@@ -105,6 +105,87 @@ void filter_symmetric_column(const std::vector<const T *> &rows, T *dst_row, siz
     }
 }
 
+// ---- the same two filters with the reference's own chunk structure, for the TIMED baseline -----------
+// The reference writes its loops over fixed-size chunks so that rustc vectorises them: rows in chunks
+// of 4 consecutive subpixels (filter_1d.rs:340-370), columns in chunks of 32 (one-byte subpixels only),
+// 16, 4 and 1 (171-316).  Restated chunk for chunk, with the multiply_accumulate flavour a template
+// parameter (src/math/utils.rs:7-47 picks it at compile time too), g++ -O3 emits packed AVX2 for them;
+// per lane the arithmetic and its order are those of the scalar checker above, so the results are
+// bit-identical (tests/test_oracle_kat.py asserts it).  The scalar functions stay the checker; these are
+// what bench.py times, so that the CPU baseline is not slower than the code it stands in for.
+template <bool FUSED> static inline float macc(float acc, float a, float b) { return FUSED ? fmaf(a, b, acc) : acc + a * b; }
+template <bool FUSED> static inline uint32_t macc(uint32_t acc, uint32_t a, uint32_t b) { return acc + a * b; }
+
+template <typename T, typename I, bool FUSED>
+void filter_symmetric_row_chunked(const T *arena, T *dst_row, size_t dst_len, const std::vector<I> &k, int N) {
+    const size_t length = k.size(), half_len = length / 2;
+    const I hc = k[half_len];
+    const I *kk = k.data();
+    size_t x = 0;
+    for (; x + 4 <= dst_len; x += 4) {  // filter_1d.rs:340-370
+        const T *src = arena + x;
+        I acc[4];
+        for (int l = 0; l < 4; ++l) acc[l] = (I)src[half_len * N + l] * hc;
+        for (size_t i = 0; i < half_len; ++i) {
+            const T *fw = src + i * N, *bw = src + (length - i - 1) * N;
+            const I c = kk[i];
+            for (int l = 0; l < 4; ++l) acc[l] = macc<FUSED>(acc[l], (I)fw[l] + (I)bw[l], c);
+        }
+        for (int l = 0; l < 4; ++l) dst_row[x + l] = Store<T, I>::to(acc[l]);
+    }
+    for (; x < dst_len; ++x) {  // 374-389
+        const T *src = arena + x;
+        I k0 = (I)src[half_len * N] * hc;
+        for (size_t i = 0; i < half_len; ++i) k0 = macc<FUSED>(k0, (I)src[i * N] + (I)src[(length - i - 1) * N], kk[i]);
+        dst_row[x] = Store<T, I>::to(k0);
+    }
+}
+
+template <typename T, typename I, bool FUSED, int W>
+static inline void column_chunk(const T *const *rows, T *dst, size_t cx, const I *kk, size_t length, size_t half_len) {
+    I acc[W];
+    const T *mid = rows[half_len] + cx;
+    const I coeff = kk[half_len];
+    for (int l = 0; l < W; ++l) acc[l] = (I)mid[l] * coeff;
+    for (size_t i = 0; i < half_len; ++i) {
+        const T *fw = rows[i] + cx, *bw = rows[length - i - 1] + cx;
+        const I c = kk[i];
+        for (int l = 0; l < W; ++l) acc[l] = macc<FUSED>(acc[l], (I)fw[l] + (I)bw[l], c);
+    }
+    for (int l = 0; l < W; ++l) dst[cx + l] = Store<T, I>::to(acc[l]);
+}
+
+template <typename T, typename I, bool FUSED>
+void filter_symmetric_column_chunked(const std::vector<const T *> &rows, T *dst_row, size_t dst_stride, const std::vector<I> &k) {
+    const size_t length = k.size(), half_len = length / 2;
+    const T *const *r = rows.data();
+    const I *kk = k.data();
+    size_t cx = 0;
+    if (sizeof(T) == 1)  // filter_1d.rs:197-243 (two stores of 16)
+        for (; cx + 32 <= dst_stride; cx += 32) {
+            column_chunk<T, I, FUSED, 16>(r, dst_row, cx, kk, length, half_len);
+            column_chunk<T, I, FUSED, 16>(r, dst_row, cx + 16, kk, length, half_len);
+        }
+    for (; cx + 16 <= dst_stride; cx += 16) column_chunk<T, I, FUSED, 16>(r, dst_row, cx, kk, length, half_len);  // 245-271
+    for (; cx + 4 <= dst_stride; cx += 4) column_chunk<T, I, FUSED, 4>(r, dst_row, cx, kk, length, half_len);     // 273-297
+    for (; cx < dst_stride; ++cx) column_chunk<T, I, FUSED, 1>(r, dst_row, cx, kk, length, half_len);             // 299-315
+}
+
+// which pair of filters a pass of filter_2d_separable runs: 0 = scalar checker, 1 = chunked, 2 = chunked + fused mac
+template <typename T, typename I>
+static inline void run_row(int mode, const T *arena, T *dst_row, size_t dst_len, const std::vector<I> &k, int N) {
+    if (mode == 0) filter_symmetric_row<T, I>(arena, dst_row, dst_len, k, N);
+    else if (mode == 1) filter_symmetric_row_chunked<T, I, false>(arena, dst_row, dst_len, k, N);
+    else filter_symmetric_row_chunked<T, I, true>(arena, dst_row, dst_len, k, N);
+}
+template <typename T, typename I>
+static inline void run_col(int mode, const std::vector<const T *> &rows, T *dst_row, size_t dst_stride, const std::vector<I> &k) {
+    if (mode == 0) filter_symmetric_column<T, I>(rows, dst_row, dst_stride, k);
+    else if (mode == 1) filter_symmetric_column_chunked<T, I, false>(rows, dst_row, dst_stride, k);
+    else filter_symmetric_column_chunked<T, I, true>(rows, dst_row, dst_stride, k);
+}
+thread_local int t_filter_mode = 0;  // set by the *_chunked entry points around their calls
+
 // KernelTransformer, filter_1d.rs:392-420
 template <typename I> I transform(float w);
 template <> uint32_t transform<uint32_t>(float w) {
@@ -134,7 +215,7 @@ void ring_queue(const T *image, T *destination, size_t width, size_t height, int
     const size_t half_kernel = column_kernel_len / 2;
 
     make_arena_row(image, row_buffer, 0, width, N, row_kernel.size());
-    filter_symmetric_row<T, I>(row_buffer.data(), buffer.data(), full_width, row_kernel, N);
+    run_row<T, I>(t_filter_mode, row_buffer.data(), buffer.data(), full_width, row_kernel, N);
     for (size_t r = 0; r < half_kernel && (r + 1) * full_width < buffer.size(); ++r)
         memcpy(&buffer[(r + 1) * full_width], &buffer[0], full_width * sizeof(T));
 
@@ -144,8 +225,7 @@ void ring_queue(const T *image, T *destination, size_t width, size_t height, int
     for (size_t y = 1; y < height + half_kernel; ++y) {
         size_t new_y = y < height ? y : (y < height - 1 ? y : height - 1);
         make_arena_row(image, row_buffer, new_y, width, N, row_kernel.size());
-        filter_symmetric_row<T, I>(row_buffer.data(), &buffer[start_ky * full_width], full_width,
-                                   row_kernel, N);
+        run_row<T, I>(t_filter_mode, row_buffer.data(), &buffer[start_ky * full_width], full_width, row_kernel, N);
         if (y >= half_kernel) {
             std::vector<const T *> rows(column_kernel_len);
             for (size_t i = 0; i < column_kernel_len; ++i) {
@@ -153,8 +233,7 @@ void ring_queue(const T *image, T *destination, size_t width, size_t height, int
                 rows[i] = &buffer[ky * full_width];
             }
             size_t dy = y - half_kernel;
-            filter_symmetric_column<T, I>(rows, destination + dy * full_width, full_width,
-                                          column_kernel);
+            run_col<T, I>(t_filter_mode, rows, destination + dy * full_width, full_width, column_kernel);
         }
         start_ky += 1;
         start_ky %= column_kernel_len;
@@ -186,7 +265,7 @@ int filter_2d_separable(const T *image, T *destination, size_t width, size_t hei
     const size_t src_stride = width * N;
     for (size_t y = 0; y < height; ++y) {
         make_arena_row(image, row_buffer, y, width, N, rk.size());
-        filter_symmetric_row<T, I>(row_buffer.data(), &transient[y * src_stride], src_stride, rk, N);
+        run_row<T, I>(t_filter_mode, row_buffer.data(), &transient[y * src_stride], src_stride, rk, N);
     }
     // virtual column padding, 102-130 and 743-755: rows above/below are row 0 / row H-1
     const size_t pad_h = ck.size() / 2;
@@ -198,7 +277,7 @@ int filter_2d_separable(const T *image, T *destination, size_t width, size_t hei
             else if ((size_t)fy >= height) fy = (int64_t)height - 1;
             rows[k] = &transient[(size_t)fy * src_stride];
         }
-        filter_symmetric_column<T, I>(rows, destination + y * src_stride, src_stride, ck);
+        run_col<T, I>(t_filter_mode, rows, destination + y * src_stride, src_stride, ck);
     }
     return 0;
 }
@@ -321,4 +400,21 @@ extern "C" int orc_gaussian_blur_dyn(const void *src, uint32_t w, uint32_t h, in
                                                      kx.data(), kx.size(), ky.data(), ky.size());
     }
     return -1;
+}
+
+// The timed baseline's entry points: the same calls with the chunked (vectorisable) filters.
+extern "C" int orc_gaussian_blur_generic_chunked(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                                                 const orc_gauss_params *p) {
+    t_filter_mode = g_orc_fused_mac ? 2 : 1;
+    const int rc = orc_gaussian_blur_generic(src, w, h, channels, dtype, dst, p);
+    t_filter_mode = 0;
+    return rc;
+}
+
+extern "C" int orc_gaussian_blur_dyn_chunked(const void *src, uint32_t w, uint32_t h, int channels, int dtype, void *dst,
+                                             const orc_gauss_params *p) {
+    t_filter_mode = g_orc_fused_mac ? 2 : 1;
+    const int rc = orc_gaussian_blur_dyn(src, w, h, channels, dtype, dst, p);
+    t_filter_mode = 0;
+    return rc;
 }

@@ -73,6 +73,13 @@ int orc_gaussian_blur_generic(const void *src, uint32_t w, uint32_t h, int chann
 /* DynamicImage::blur / blur_advanced: Q0.15 for u8 and u16, f32 engine for f32 */
 int orc_gaussian_blur_dyn(const void *src, uint32_t w, uint32_t h, int channels,
                           int dtype, void *dst, const orc_gauss_params *p);
+/* The same two calls through filters restated with the reference's own 4- / 16- / 32-wide chunk
+ * structure (filter_1d.rs:171-316, 340-370) so that g++ vectorises them as rustc does: what the
+ * TIMED CPU baseline runs.  Bit-identical to the scalar checker above. */
+int orc_gaussian_blur_generic_chunked(const void *src, uint32_t w, uint32_t h, int channels,
+                                      int dtype, void *dst, const orc_gauss_params *p);
+int orc_gaussian_blur_dyn_chunked(const void *src, uint32_t w, uint32_t h, int channels,
+                                  int dtype, void *dst, const orc_gauss_params *p);
 /* Q15 transform + strip of zero ends; returns scanned length (filter_1d.rs:396-437) */
 int orc_q15_kernel(const float *k, int n, uint32_t *out);
 

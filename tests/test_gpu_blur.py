@@ -26,15 +26,60 @@ def _gauss_check(img, p, cuda, host=False):
     flags_dyn = L.FP_FAST if img.dtype != np.float32 else L.FP_STRICT
     got = get(imageops.blur_dyn(src, p, flags=flags_dyn))
     assert got.tobytes() == want_dyn.tobytes(), f"dyn path differs {img.dtype} {img.shape} {p}"
+    for fl in (L.GAUSS_TWO_KERNELS, L.GAUSS_FUSED):   # the row / column kernel pair and the fused kernel, whatever the library would pick
+        got = get(imageops.blur_dyn(src, p, flags=flags_dyn | fl))
+        assert got.tobytes() == want_dyn.tobytes(), f"dyn path (flag {fl}) differs {img.dtype} {img.shape} {p}"
     # generic path: f32 engine; STRICT bit-exact, FAST within tolerance
     want = o.gaussian_blur(img, _oparams(p), "generic")
     got = get(imageops.blur_advanced(src, p, flags=L.FP_STRICT))
     assert got.tobytes() == want.tobytes(), f"generic strict differs {img.dtype} {img.shape} {p}"
-    fast = get(imageops.blur_advanced(src, p))
-    if img.dtype == np.float32:
-        assert np.allclose(fast, want, rtol=1e-5, atol=1e-6)
-    else:
-        assert np.abs(fast.astype(np.int64) - want.astype(np.int64)).max() <= 1
+    for fl in (L.FP_FAST, L.FP_FAST | L.GAUSS_TWO_KERNELS, L.FP_FAST | L.GAUSS_FUSED):   # the library's pick, the kernel pair, the fused kernel
+        fast = get(imageops.blur_advanced(src, p, flags=fl))
+        if img.dtype == np.float32:
+            assert np.allclose(fast, want, rtol=1e-5, atol=1e-6)
+        else:
+            assert np.abs(fast.astype(np.int64) - want.astype(np.int64)).max() <= 1
+
+
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_gaussian_fused_kernel_shapes(cuda, dtype, c, monkeypatch):
+    """The fused kernel's geometry: several strips with a ragged last one, CTA ranges that begin and end inside
+    strips (forced CTA counts), every remainder of the 16-tap steps (3 ... 101 taps), images smaller than a strip /
+    a chunk, odd row pitches."""
+    rng = np.random.default_rng(60 + c)
+    img = rand_image(rng, 150, 333 if c < 3 else 131, c, dtype)
+    for sigma in (0.5, 0.8, 1.2, 1.5, 2.0, 3.5, 10.0, 15.5):   # 3, 5, 5, 7, 11, 21, 65, 101 taps
+        _gauss_check(img, GaussianBlurParameters.new_from_sigma(sigma), cuda)
+    for ctas in ("1", "7", "1000"):
+        monkeypatch.setenv("B200IMG_GF_CTAS", ctas)
+        _gauss_check(img, GaussianBlurParameters.new_from_sigma(4.0), cuda)
+        _gauss_check(rand_image(rng, 37, 21, c, dtype), GaussianBlurParameters.new_anisotropic_kernel_size(15.0, 41.0), cuda)
+    monkeypatch.delenv("B200IMG_GF_CTAS")
+    _gauss_check(rand_image(rng, 3, 500, c, dtype), GaussianBlurParameters.new_from_sigma(3.0), cuda)
+    _gauss_check(rand_image(rng, 300, 2, c, dtype), GaussianBlurParameters.new_from_sigma(3.0), cuda)
+
+
+def test_gaussian_fused_batch_4k_band_vs_oracle(cuda):
+    """The timed configuration itself (8 x 3840x2160 Rgb8, sigma 10, both engines): a 96-row band of the first and
+    of the last image against the oracle (which needs the band plus 32 rows either side)."""
+    import ctypes as C
+    import torch
+    lib = L.lib()
+    base = bench_image(3840, 2160, 3)
+    batch = np.stack([np.roll(base, 37 * i, axis=1) for i in range(8)])
+    src = torch.from_numpy(batch).to(cuda)
+    dst = torch.empty_like(src)
+    p = GaussianBlurParameters.new_from_sigma(10.0)
+    stream = torch.cuda.current_stream().cuda_stream
+    for path, name in ((L.BLUR_GENERIC, "generic"), (L.BLUR_DYN, "dyn")):
+        L.check(lib.b200img_gaussian_blur_batch_dev(src.data_ptr(), 3840, 2160, 3, L.U8, dst.data_ptr(), 8, C.byref(p.raw), path, L.FP_FAST, stream))
+        out = dst.cpu().numpy()
+        for i, (y0, y1) in ((0, (0, 96)), (7, (2064, 2160)), (3, (1000, 1096))):
+            lo, hi = max(0, y0 - 32), min(2160, y1 + 32)
+            want = o.gaussian_blur(np.ascontiguousarray(batch[i, lo:hi]), _oparams(p), name)[y0 - lo:y1 - lo]
+            d = np.abs(out[i, y0:y1].astype(int) - want.astype(int)).max()
+            assert d <= (1 if path == L.BLUR_GENERIC else 0), (name, i, y0, d)
 
 
 @pytest.mark.parametrize("dtype", DT)
