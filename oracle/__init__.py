@@ -349,3 +349,37 @@ def alpha_mul(img, un: bool):
     h, w, c = a.shape
     lib().orc_alpha_mul(_ptr(a), h * w, c, _DT[a.dtype], int(un))
     return a
+
+
+def resize_region(fetch_rows, w: int, h: int, c: int, dtype, nw: int, nh: int, f, y0: int, y1: int, x0: int, x1: int,
+                  acc_init: float = 1.0):
+    """Destination window [y0, y1) x [x0, x1) of imageops::resize of a w x h image that is too large to run whole:
+    the C oracle's own weight tables (orc_resize_weights) applied by numpy in the reference's order -- vertical
+    pass first with the accumulator starting at `acc_init`, every multiply and add rounded separately to f32, taps
+    ascending (sample.rs:546-558), then the horizontal pass from 0 (310-334), then clamp_nearest_from.
+    `fetch_rows(r0, r1, c0, c1)` returns source rows [r0, r1), columns [c0, c1) as an array (rows, cols, c).
+    Bit-identical with resize() on images small enough for both (tests/test_oracle_kat.py)."""
+    dtype = np.dtype(dtype)
+    vl, vc, vw = resize_weights(f, h, nh, 0)
+    hl, hc, hw = resize_weights(f, w, nw, 1)
+    r0, r1 = int(vl[y0]), int(vl[y1 - 1] + vc[y1 - 1])
+    c0, c1 = int(hl[x0]), int(hl[x1 - 1] + hc[x1 - 1])
+    src = np.asarray(fetch_rows(r0, r1, c0, c1)).astype(np.float32)           # exact for u8 / u16
+    F = np.float32
+    tmp = np.empty((y1 - y0, c1 - c0, c), np.float32)
+    for oy in range(y0, y1):
+        acc = np.full((c1 - c0, c), F(acc_init), np.float32)
+        for i in range(int(vc[oy])):
+            acc = acc + src[int(vl[oy]) - r0 + i] * vw[oy, i]
+        tmp[oy - y0] = acc
+    out = np.empty((y1 - y0, x1 - x0, c), np.float32)
+    for ox in range(x0, x1):
+        acc = np.zeros((y1 - y0, c), np.float32)
+        for i in range(int(hc[ox])):
+            acc = acc + tmp[:, int(hl[ox]) - c0 + i] * hw[ox, i]
+        out[:, ox - x0] = acc
+    if dtype == np.float32:
+        return np.minimum(np.maximum(out, F(0.0)), F(1.0))   # max(0).min(1); a NaN sample is not expected here
+    mx = np.iinfo(dtype).max
+    v = out + F(0.5)
+    return np.where(np.isnan(v), 0, np.clip(np.trunc(v), 0, mx)).astype(dtype)
