@@ -22,6 +22,8 @@
 //                    each lane slides its sums along a 64-pixel chunk; results go
 //                    back through shared memory so global stores are contiguous.
 #include "common.cuh"
+
+#include <cstdlib>
 #include "host_tables.h"
 
 #include <mutex>
@@ -32,6 +34,10 @@ namespace b200 {
 // boxblur_u8.cu: word-at-a-time passes for u8 images (the common case)
 int box_pass_u8(const uint8_t *src, uint8_t *tmp, uint8_t *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t radius,
                 const DeviceCtx *ctx, cudaStream_t st);
+// boxblur_u8.cu: both passes of a box in one kernel (the horizontally blurred rows stay in shared memory)
+bool box_fused_u8_applies(uint32_t w, int C, uint32_t radius, const void *a, const void *b, const void *c, const DeviceCtx *ctx);
+int box_fused_u8(const uint8_t *src, uint8_t *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t radius,
+                 const DeviceCtx *ctx, cudaStream_t st);
 
 namespace {
 
@@ -308,6 +314,20 @@ int run(const void *src, void *dst, void *tmp, uint32_t w, uint32_t h, int C, ui
         const DeviceCtx *ctx, cudaStream_t st) {
     const size_t total_rows = (size_t)h * n_images;
     const T *cur = (const T *)src;
+    if constexpr (std::is_same<T, uint8_t>::value) {
+        // three fused kernels, src -> dst -> tmp -> dst: one read and one write of the image per box
+        bool fused = getenv("B200IMG_BOX_UNFUSED") == nullptr && src != dst;  // (in place: the first box would read rows other CTAs overwrite)
+        for (int pass = 0; pass < 3 && fused; ++pass) fused = box_fused_u8_applies(w, C, radii[pass], src, tmp, dst, ctx);
+        if (fused) {
+            const uint8_t *from[3] = {(const uint8_t *)src, (const uint8_t *)dst, (const uint8_t *)tmp};
+            uint8_t *to[3] = {(uint8_t *)dst, (uint8_t *)tmp, (uint8_t *)dst};
+            for (int pass = 0; pass < 3; ++pass) {
+                const int rc = box_fused_u8(from[pass], to[pass], w, h, C, n_images, radii[pass], ctx, st);
+                if (rc != 1) return rc < 0 ? rc : fail(B200IMG_ERR_CUDA, "fast_blur: fused box kernel declined after accepting");
+            }
+            return B200IMG_OK;
+        }
+    }
     for (int pass = 0; pass < 3; ++pass) {
         BoxGeom g;
         g.w = w; g.h = h; g.C = (uint32_t)C;

@@ -17,6 +17,9 @@
 // Taken when ks <= 255 and rows are 4-byte aligned; boxblur.cu's generic kernels cover the rest.
 #include "common.cuh"
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace b200 {
 namespace {
 
@@ -205,7 +208,266 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
 
 int odd_words(int bytes) { return (((bytes + 3) / 4) | 1); }
 
+// ---- horizontal + vertical pass of one box in one kernel ---------------------------------------------
+// The two-kernel form writes the horizontally blurred image to HBM and reads it back: per box 4 bytes of
+// traffic per subpixel for a 1-byte-in / 1-byte-out operator.  Here a CTA owns a strip of F_XT pixels and
+// streams down a band of rows in chunks of 32: (1) the chunk's source rows (+ r pixels either side) are
+// staged by asynchronous word copies; (2) the HORIZONTAL pass (lane = row, warp = chunk of F_XC pixels,
+// sliding sums as above) writes its quantised u8 rows into a ring of rows in shared memory; (3) the
+// VERTICAL pass (thread = one word column, the four running sums in two registers as 16-bit lanes) takes
+// the chunk's rows from the ring one by one: emit a destination row, add the incoming row, subtract the
+// row 2r + 1 back.  Running sums persist from chunk to chunk, so inside a band nothing is computed twice;
+// a band primes its window with 2r + 1 rows.  The quantised store between the passes is the reference's
+// (fast_blur.rs:36-71), so the result stays bit-identical.  Rows above / below the image are the first /
+// last row (fast_blur.rs:416-473): ring row q holds the horizontal pass of source row clamp(q).
+constexpr int F_XT = 128;      // strip width in pixels: small enough for four or five CTAs per SM, which overlap one another's staging waits
+constexpr int F_XC = 32;       // pixels per horizontal-pass warp item
+constexpr int F_WARPS = F_XT / F_XC;
+constexpr int F_THREADS = F_WARPS * 32;
+constexpr int F_CH = 32;       // rows per chunk = lanes of the horizontal pass
+
+struct FusedBoxArgs {
+    const uint8_t *src;
+    uint8_t *dst;
+    U8Geom g;
+    int bands, band_rows;      // rows of a band (the last may be shorter)
+    int in_pitch, ring_pitch;  // words per staged row / ring row (odd)
+    int ring_rows;             // multiple of 32, >= 32 + 2r + 1
+};
+
+template <int C>
+__global__ void __launch_bounds__(F_THREADS)
+box_fused_u8_kernel(const FusedBoxArgs a) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    uint32_t *s_in = sm;                                    // [32][in_pitch]
+    uint32_t *ring = sm + (size_t)F_CH * a.in_pitch;        // [ring_rows][ring_pitch]
+    const uint32_t s_in_u32 = (uint32_t)__cvta_generic_to_shared(s_in);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const U8Geom &g = a.g;
+    const int r = (int)g.r, W = (int)g.w, H = (int)g.h, ks = (int)g.ks;
+    const int x0 = blockIdx.x * F_XT;
+    const int band = blockIdx.y % a.bands;
+    const size_t img = blockIdx.y / a.bands;
+    const int b0 = band * a.band_rows, b1 = min(b0 + a.band_rows, H);
+    if (b0 >= b1) return;
+    const int tw = min(F_XT, W - x0);
+    const int sp = tw + 2 * r;
+    const int sbytes = sp * C;
+    const size_t g_pitch = (size_t)W * C;                   // bytes; multiple of 4 (checked by the host)
+    const uint8_t *src = a.src + img * (size_t)H * g_pitch;
+    uint8_t *dst = a.dst + img * (size_t)H * g_pitch;
+    // A staged row = sp pixels from source pixel x0 - r, clamped at the image's edges.  The pixels inside the image are
+    // one contiguous span of the source row: it is copied with asynchronous copies of ALIGNED global words (every copy
+    // of the chunk in flight at once); the staged row's byte phase is chosen so that the span lands on the same byte
+    // phase in shared memory, and is taken out by funnel shifts when the words are used.  The clamped pixels (edge
+    // strips only) are filled from the span's first / last pixel afterwards.
+    const int lo_px = max(x0 - r, 0), hi_px = min(x0 + tw + r, W);
+    const int e_off = (lo_px - (x0 - r)) * C, n_in = (hi_px - lo_px) * C;     // the span's place and length in the staged row (bytes)
+    const int a_g = (int)(reinterpret_cast<uintptr_t>(src + (size_t)lo_px * C) & 3);  // the span's phase in global memory (same for every row)
+    const int phase = (a_g - e_off) & 3;                                        // staged byte i lives at shared byte phase + i
+    const int span_words = (a_g + n_in + 3) / 4;
+    const int span_w0 = (phase + e_off - a_g) / 4;                              // first shared word the span's words go to
+    const int owords = (tw * C + 3) / 4;                    // destination words of a strip row (tw * C is a multiple of 4 unless the row ends)
+    const int q0 = b0 - r;                                  // source row (before clamping) of ring row 0
+    const int nq = (b1 - b0) + 2 * r + 1;                   // ring rows the band consumes (the last one only triggers the last emit)
+    const int nchunks = (nq + F_CH - 1) / F_CH;
+    const int pshift = phase * 8, nbyte = ((2 * r + 1) * C + phase) & 3;
+    const int hchunks = (tw + F_XC - 1) / F_XC;
+
+    // vertical state of this thread's word column
+    uint32_t se = g.bias | (g.bias << 16), so = se;
+    uint32_t *dcol = reinterpret_cast<uint32_t *>(dst + (size_t)b0 * g_pitch + (size_t)x0 * C) + tid;
+    const size_t dwords = g_pitch / 4;
+    int primed = 0;     // rows added so far (the window is full at ks)
+    int out_left = b1 - b0;
+
+    for (int ci = 0; ci < nchunks; ++ci) {
+        // ---- (1) stage the chunk's source rows ----
+        for (int rr = warp; rr < F_CH; rr += F_WARPS) {
+            const int y = min(max(q0 + ci * F_CH + rr, 0), H - 1);
+            const uint32_t *gw = reinterpret_cast<const uint32_t *>(src + (size_t)y * g_pitch + (size_t)lo_px * C - a_g) + lane;
+            uint32_t d = s_in_u32 + (uint32_t)((rr * a.in_pitch + span_w0 + lane) * 4);
+#pragma unroll 4
+            for (int wi = lane; wi < span_words; wi += 32, gw += 32, d += 128)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gw) : "memory");
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        if (n_in < sbytes) {   // an edge strip: replicate the span's first / last pixel outwards (each warp on its own rows)
+            __syncwarp();
+            for (int rr = warp; rr < F_CH; rr += F_WARPS) {
+                uint8_t *sb = reinterpret_cast<uint8_t *>(s_in + (size_t)rr * a.in_pitch) + phase;
+                for (int e = lane; e < e_off; e += 32) sb[e] = sb[e_off + e % C];
+                const int right0 = e_off + n_in;
+                for (int e = right0 + lane; e < sbytes; e += 32) sb[e] = sb[right0 - C + (e - right0) % C];
+            }
+        }
+        __syncthreads();
+
+        // ---- (2) horizontal pass: lane = row of the chunk, item = F_XC-pixel piece; output into the ring ----
+        {
+            const uint32_t *in_row = s_in + (size_t)lane * a.in_pitch;
+            uint32_t *out_row = ring + (size_t)((ci * F_CH) % a.ring_rows + lane) * a.ring_pitch;
+            for (int ck = warp; ck < hchunks; ck += F_WARPS) {
+                const int xa = ck * F_XC, xb = min(xa + F_XC, tw);
+                uint32_t sum[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) sum[c] = g.bias;
+                {
+                    const uint8_t *b = reinterpret_cast<const uint8_t *>(in_row) + phase + xa * C;
+                    for (int j = 0; j <= 2 * r; ++j) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) sum[c] += b[j * C + c];
+                    }
+                }
+                const uint32_t *pw = in_row + (xa * C + phase) / 4;                    // outgoing pixels, aligned down
+                const uint32_t *nw = in_row + ((xa + 2 * r + 1) * C + phase) / 4;      // incoming pixels, aligned down
+                for (int x = xa; x < xb; x += 4) {
+                    uint32_t prev[C], next[C], praw[C + 1], nraw[C + 1];
+#pragma unroll
+                    for (int k = 0; k <= C; ++k) { praw[k] = pw[k]; nraw[k] = nw[k]; }
+#pragma unroll
+                    for (int k = 0; k < C; ++k) {
+                        prev[k] = __funnelshift_r(praw[k], praw[k + 1], pshift);
+                        next[k] = __funnelshift_r(nraw[k], nraw[k + 1], nbyte * 8);
+                    }
+                    uint32_t ob[4 * C];
+#pragma unroll
+                    for (int b = 0; b < 4 * C; ++b) {
+                        const int c = b % C;
+                        ob[b] = __umulhi(sum[c], g.recip);
+                        sum[c] = sum[c] + byte_of(next[b / 4], b & 3) - byte_of(prev[b / 4], b & 3);
+                    }
+                    uint32_t *ow = out_row + (x * C) / 4;
+#pragma unroll
+                    for (int k = 0; k < C; ++k)
+                        ow[k] = __byte_perm(__byte_perm(ob[4 * k], ob[4 * k + 1], 0x0040), __byte_perm(ob[4 * k + 2], ob[4 * k + 3], 0x0040), 0x5410);
+                    pw += C;
+                    nw += C;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- (3) vertical pass over the chunk's ring rows ----
+        if (tid < owords) {
+            const int rows_here = min(F_CH, nq - ci * F_CH);
+            const int slot = (ci * F_CH) % a.ring_rows;                 // ring row of the chunk's first incoming row
+            // the row leaving the window when ring row q comes in is q - ks; while the window fills, nothing leaves
+            const int fill = min(max(ks - primed, 0), rows_here);        // rows of this chunk that only fill the window
+            int back = slot + fill - ks;
+            if (back < 0) back += a.ring_rows;
+            const uint32_t *rin = ring + (size_t)slot * a.ring_pitch + tid;
+            const uint32_t *rout = ring + (size_t)back * a.ring_pitch + tid;
+            const uint32_t *rend = ring + (size_t)a.ring_rows * a.ring_pitch + tid;
+            const size_t ring_span = (size_t)a.ring_rows * a.ring_pitch;
+            const int pitch = a.ring_pitch;
+            auto emit = [&]() {
+                const uint32_t o0 = __umulhi(se & 0xffffu, g.recip), o2 = __umulhi(se >> 16, g.recip);
+                const uint32_t o1 = __umulhi(so & 0xffffu, g.recip), o3 = __umulhi(so >> 16, g.recip);
+                *dcol = __byte_perm(__byte_perm(o0, o1, 0x0040), __byte_perm(o2, o3, 0x0040), 0x5410);  // tw * C is a multiple of 4: whole words only
+                dcol += dwords;
+            };
+            // (a chunk's incoming rows never wrap: chunks and the ring are multiples of 32 rows)
+            for (int k = 0; k < fill; ++k, ++primed) {   // filling the window (first chunk(s) of a band only)
+                const uint32_t vin = *rin;
+                se += even_lanes(vin);
+                so += odd_lanes(vin);
+                rin += pitch;
+            }
+            // steady state: every row emits a destination row (while the band has any left) and slides the window.
+            // The outgoing rows wrap at most once inside the chunk: two segments, no per-row wrap test; eight rows
+            // at a time with their sixteen loads issued first (a load-use-per-row loop serialises on the shared-
+            // memory latency, which the few warps of the vertical pass cannot hide).
+            int m = rows_here - fill;
+            while (m > 0) {
+                const int seg = min(m, (int)((rend - rout) / pitch));
+                const int e = min(seg, out_left);
+                int i = 0;
+                constexpr int VU = 8;
+                for (; i + VU <= e; i += VU) {
+                    uint32_t vin[VU], vout[VU];
+#pragma unroll
+                    for (int u = 0; u < VU; ++u) { vin[u] = rin[u * pitch]; vout[u] = rout[u * pitch]; }
+#pragma unroll
+                    for (int u = 0; u < VU; ++u) {
+                        emit();
+                        se = se + even_lanes(vin[u]) - even_lanes(vout[u]);
+                        so = so + odd_lanes(vin[u]) - odd_lanes(vout[u]);
+                    }
+                    rin += VU * pitch;
+                    rout += VU * pitch;
+                }
+                for (; i < seg; ++i) {
+                    const uint32_t vin = *rin, vout = *rout;
+                    if (i < e) emit();
+                    se = se + even_lanes(vin) - even_lanes(vout);
+                    so = so + odd_lanes(vin) - odd_lanes(vout);
+                    rin += pitch;
+                    rout += pitch;
+                }
+                out_left -= e;
+                m -= seg;
+                if (rout >= rend) rout -= ring_span;
+            }
+        }
+        __syncthreads();   // the next chunk's staging and horizontal pass reuse s_in and the oldest ring rows
+    }
+}
+
+
+
 }  // namespace
+
+// One box (both passes in one kernel) on u8 images, src -> dst.  Returns 1 if done, 0 if the fused kernel does not
+// apply (the caller then runs box_pass_u8 or the generic kernels for ALL three boxes), < 0 on error.
+bool box_fused_u8_applies(uint32_t w, int C, uint32_t radius, const void *a, const void *b, const void *c, const DeviceCtx *ctx) {
+    const uint32_t ks = 2 * radius + 1;
+    if (ks > 255 || ((size_t)w * C) % 4 != 0) return false;
+    if (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 3) != 0) return false;
+    const int in_pitch = odd_words((F_XT + 2 * (int)radius + 1 + 8) * C + 8), ring_pitch = odd_words(F_XT * C + 4);
+    const int ring_rows = (F_CH + (int)ks + F_CH - 1) / F_CH * F_CH;
+    return ((size_t)F_CH * in_pitch + (size_t)ring_rows * ring_pitch) * 4 <= std::min<size_t>(ctx->smem_optin, 110 * 1024);  // at least two CTAs per SM
+}
+
+int box_fused_u8(const uint8_t *src, uint8_t *dst, uint32_t w, uint32_t h, int C, uint32_t n_images, uint32_t radius,
+                 const DeviceCtx *ctx, cudaStream_t st) {
+    FusedBoxArgs a;
+    a.src = src; a.dst = dst;
+    a.g.w = w; a.g.h = h; a.g.r = radius; a.g.ks = 2 * radius + 1;
+    a.g.recip = UINT32_MAX / a.g.ks + 1u;
+    a.g.bias = a.g.ks / 2;
+    a.in_pitch = odd_words((F_XT + 2 * (int)radius + 1 + 8) * C + 8);  // slack: the last 4-pixel step reads up to C + 1 words past the last incoming pixel
+    a.ring_pitch = odd_words(F_XT * C + 4);
+    a.ring_rows = (F_CH + (int)a.g.ks + F_CH - 1) / F_CH * F_CH;
+    const size_t smem = ((size_t)F_CH * a.in_pitch + (size_t)a.ring_rows * a.ring_pitch) * 4;
+    const unsigned strips = (w + F_XT - 1) / F_XT;
+    // bands: each primes its window with 2r + 1 extra rows.  A CTA runs its chunks as a chain of short phases, so the
+    // GPU needs many of them in flight: about ten per SM (measured on B200: 8 x 4K Rgb8 0.96 ms with 2 bands, 0.73 ms
+    // with 6), while a band stays at least four windows (and 64 rows) long so the priming stays a small share.
+    int bands = 1;
+    const int min_rows = std::max(64, 4 * (int)a.g.ks);
+    while ((uint64_t)strips * n_images * bands < 10ull * ctx->sm_count && (int)(h / (bands + 1)) >= min_rows) ++bands;
+    if (const char *e = getenv("B200IMG_BOX_BANDS")) { const int v = atoi(e); if (v >= 1) bands = std::min<int>(v, (int)h); }
+    a.band_rows = (int)((h + bands - 1) / bands);
+    a.bands = (int)((h + a.band_rows - 1) / a.band_rows);
+    if ((uint64_t)a.bands * n_images > 65535) return 0;
+    const dim3 grid(strips, (unsigned)(a.bands * n_images));
+#define F_GO(CC)                                                                                        \
+    {                                                                                                   \
+        auto k = box_fused_u8_kernel<CC>;                                                               \
+        B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+        k<<<grid, F_THREADS, smem, st>>>(a);                                                            \
+    }
+    switch (C) {
+        case 1: F_GO(1) break;
+        case 2: F_GO(2) break;
+        case 3: F_GO(3) break;
+        default: F_GO(4) break;
+    }
+#undef F_GO
+    B200_CUDA(cudaGetLastError());
+    return 1;
+}
 
 // One box pass (horizontal into tmp, vertical into dst) on u8 images.  Returns 1 if done, 0 if the
 // fast path does not apply (caller uses the generic kernels), < 0 on error.

@@ -151,6 +151,33 @@ def test_fast_blur_all_types(cuda, dtype, c):
             assert got.tobytes() == want.tobytes(), (dtype, c, sigma)
 
 
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+def test_fast_blur_u8_fused_and_unfused_kernels(cuda, c, monkeypatch):
+    """u8 images take one fused kernel per box (horizontal rows kept in a shared-memory ring) or, where that does
+    not apply, a horizontal and a vertical kernel: both against the oracle, over several strips (ragged last one),
+    several bands (forced), windows longer than the image, radii up to the fused kernel's limit and beyond it."""
+    import torch
+    rng = np.random.default_rng(70 + c)
+    shapes = [(150, 600 if c < 4 else 300), (70, 257), (9, 40), (300, 8)]
+    for h, w in shapes:
+        if (w * c) % 4:
+            w += 4 - (w * c) % 4 if c != 3 else 4 - w % 4   # the word-wise kernels need rows of whole words; other widths take the generic ones
+        img = rand_image(rng, h, w, c, np.uint8)
+        dev = torch.from_numpy(img).to(cuda)
+        for sigma in (0.5, 3.0, 10.0, 22.0, 60.0):
+            want = o.fast_blur(img, sigma)
+            for bands in (None, "1", "5"):
+                if bands is None:
+                    monkeypatch.delenv("B200IMG_BOX_BANDS", raising=False)
+                else:
+                    monkeypatch.setenv("B200IMG_BOX_BANDS", bands)
+                assert np.array_equal(imageops.fast_blur(dev, sigma).cpu().numpy(), want), (h, w, c, sigma, bands)
+            monkeypatch.delenv("B200IMG_BOX_BANDS", raising=False)
+            monkeypatch.setenv("B200IMG_BOX_UNFUSED", "1")
+            assert np.array_equal(imageops.fast_blur(dev, sigma).cpu().numpy(), want), (h, w, c, sigma, "unfused")
+            monkeypatch.delenv("B200IMG_BOX_UNFUSED")
+
+
 def test_fast_blur_k2_reduced_and_host(cuda):
     img = bench_image(3840, 2160, 3)[300:800, 200:1100].copy()
     assert np.array_equal(imageops.fast_blur(img, 10.0), o.fast_blur(img, 10.0))
