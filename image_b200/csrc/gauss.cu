@@ -142,6 +142,36 @@ int run(const void *src, void *dst, void *mid, const uint32_t *d_rk, const uint3
 
 }  // namespace
 
+// Rows [dst_row0, dst_row0 + dst_rows) of the blur of a w x h image, from a buffer holding its source rows
+// [src_row0, src_row0 + src_rows) (which must include the rows those read), into a buffer whose row 0 is row
+// dst_row0: the fused kernel's row window (no scratch, no copy).  Returns 1 when the fused kernel does not cover
+// the case (the caller blurs a haloed band into scratch instead).
+int gaussian_blur_rows_launch(const void *src_band, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h, int C, int dtype,
+                              void *dst_band, uint32_t dst_row0, uint32_t dst_rows, const b200img_gauss_params *p, int path, int flags,
+                              cudaStream_t st) {
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    const bool q15 = path == B200IMG_BLUR_DYN && dtype != B200IMG_F32;
+    const bool strict = (flags & B200IMG_FP_STRICT) != 0;
+    if (!((q15 && dtype == B200IMG_U8) || (!q15 && !strict)) || (flags & B200IMG_GAUSS_TWO_KERNELS)) return 1;
+    const std::vector<float> kx = gaussian_kernel_1d(p->x_kernel_size, p->x_sigma);
+    const std::vector<float> ky = gaussian_kernel_1d(p->y_kernel_size, p->y_sigma);
+    std::vector<uint32_t> rk, ck;
+    if (q15) {
+        rk = q15_scanned_kernel(kx);
+        ck = q15_scanned_kernel(ky);
+    } else {
+        for (float v : f32_scanned_kernel(kx)) { uint32_t b; memcpy(&b, &v, 4); rk.push_back(b); }
+        for (float v : f32_scanned_kernel(ky)) { uint32_t b; memcpy(&b, &v, 4); ck.push_back(b); }
+    }
+    const int rl = (int)rk.size(), cl = (int)ck.size();
+    switch (dtype) {
+        case B200IMG_U8: return gauss_fused_run<uint8_t>((const uint8_t *)src_band, (uint8_t *)dst_band, w, h, C, 1, src_row0, src_rows, dst_row0, dst_rows, rk.data(), rl, ck.data(), cl, q15, true, ctx, st);
+        case B200IMG_U16: return gauss_fused_run<uint16_t>((const uint16_t *)src_band, (uint16_t *)dst_band, w, h, C, 1, src_row0, src_rows, dst_row0, dst_rows, rk.data(), rl, ck.data(), cl, q15, true, ctx, st);
+        default: return gauss_fused_run<float>((const float *)src_band, (float *)dst_band, w, h, C, 1, src_row0, src_rows, dst_row0, dst_rows, rk.data(), rl, ck.data(), cl, q15, true, ctx, st);
+    }
+}
+
 // image_top = false: row 0 of `src` is not the image's first row (a row band of a larger image), so the
 // 1-tap ring-queue quirk, which is about the image's row 0, does not apply to it.
 int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
@@ -172,10 +202,6 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
 
     size_t total;
     if (!checked_mul(w, h, (size_t)C, n_images, &total)) return fail(B200IMG_ERR_DIMENSION, "gaussian_blur: size overflows");
-    const size_t mid_elem = q15 ? dtype_size(dtype) : 4;
-    void *mid;
-    int rc = scratch(SCRATCH_A, total * mid_elem, &mid);
-    if (rc) return rc;
 
     const bool strict = (flags & B200IMG_FP_STRICT) != 0;
     // One kernel for both passes (gauss_fused.cu) wherever reordering the sum is allowed and the job is one it
@@ -190,6 +216,11 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
         else fr = gauss_fused_run<float>((const float *)src, (float *)dst, w, h, C, n_images, 0, h, 0, h, rk.data(), rl, ck.data(), cl, q15, force, ctx, st);
         if (fr != 1) return fr;
     }
+    // the kernel pairs below keep the intermediate image in device scratch
+    const size_t mid_elem = q15 ? dtype_size(dtype) : 4;
+    void *mid;
+    int rc = scratch(SCRATCH_A, total * mid_elem, &mid);
+    if (rc) return rc;
     if ((q15 || !strict) && rk.size() <= (size_t)GT_MAX_TAPS && ck.size() <= (size_t)GT_MAX_TAPS) {
         const int rl = (int)rk.size(), cl = (int)ck.size();
 #define TILED(T, Mid, Acc)                                                                                                  \

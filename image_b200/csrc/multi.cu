@@ -34,6 +34,9 @@ int gaussian_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dty
                          const b200img_gauss_params *p, int path, int flags, cudaStream_t st, bool image_top = true);
 int fast_blur_launch(const void *src, uint32_t w, uint32_t h, int C, int dtype, void *dst, uint32_t n_images,
                      float sigma, cudaStream_t st);
+int gaussian_blur_rows_launch(const void *src_band, uint32_t src_row0, uint32_t src_rows, uint32_t w, uint32_t h, int C, int dtype,
+                              void *dst_band, uint32_t dst_row0, uint32_t dst_rows, const b200img_gauss_params *p, int path, int flags,
+                              cudaStream_t st);
 
 namespace {
 
@@ -270,6 +273,17 @@ int b200img_gaussian_blur_band_dev(const void *d_src_band, uint32_t src_row0, ui
         return fail(B200IMG_ERR_BAD_ARG, "gaussian_blur_band: kernel sizes must be odd (%u, %u)", p->x_kernel_size, p->y_kernel_size);
     const cudaStream_t st = (cudaStream_t)stream;
     ScratchScope scope(st);
+    // large bands of long kernels: the fused kernel computes exactly the band's rows from the band buffer (it clamps
+    // at the IMAGE's edges itself); everything else blurs the haloed band as an image and keeps the band's rows
+    if (dst_rows && row_bytes && d_src_band && d_dst_band && dst_row0 + (uint64_t)dst_rows <= h && src_row0 + (uint64_t)src_rows <= h &&
+        (uint64_t)dst_rows * w >= (1u << 20) && p->x_kernel_size + p->y_kernel_size >= 64) {
+        uint32_t lo, n;
+        blur_need(h, gauss_halo(p), dst_row0, dst_rows, &lo, &n);
+        if (lo >= src_row0 && lo + (uint64_t)n <= src_row0 + (uint64_t)src_rows) {
+            rc = gaussian_blur_rows_launch(d_src_band, src_row0, src_rows, w, h, C, dtype, d_dst_band, dst_row0, dst_rows, p, path, flags, st);
+            if (rc != 1) return rc;
+        }
+    }
     return blur_band("gaussian_blur_band", d_src_band, src_row0, src_rows, h, row_bytes, d_dst_band, dst_row0, dst_rows, gauss_halo(p), st,
                      [&](const void *s, uint32_t rows, void *d, bool top) {
                          return gaussian_blur_launch(s, w, rows, C, dtype, d, 1, p, path, flags, st, top);

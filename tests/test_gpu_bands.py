@@ -54,6 +54,22 @@ def test_gaussian_bands(cuda):
             assert np.allclose(fast, want, rtol=1e-5, atol=1e-6)
 
 
+def test_gaussian_bands_large_through_the_fused_row_window(cuda):
+    """Bands of a large image with a long kernel run the fused kernel on exactly the band's rows (no scratch, no
+    copy): the stitched result equals the whole-image result bit for bit (Q0.15) / the oracle within +-1 (f32 engine)."""
+    rng = np.random.default_rng(6)
+    img = rng.integers(0, 256, (2100, 1536, 3), dtype=np.uint8)
+    p = GaussianBlurParameters.new_from_sigma(10.0)
+    whole_q = imageops.blur_dyn(img, p)
+    whole_f = imageops.blur_advanced(img, p)
+    for devs in _device_sets()[1:]:
+        assert np.array_equal(run_bands("gaussian", img, devs, params=p, path=L.BLUR_DYN), whole_q), devs
+        assert np.array_equal(run_bands("gaussian", img, devs, params=p, path=L.BLUR_GENERIC), whole_f), devs
+    band = slice(690, 760)   # across the first seam of the three-band split
+    want = o.gaussian_blur(np.ascontiguousarray(img[band.start - 32:band.stop + 32]), o.gauss_params_from_sigma(10.0), "dyn")[32:-32]
+    assert np.array_equal(whole_q[band], want)
+
+
 def test_fast_blur_bands(cuda):
     rng = np.random.default_rng(5)
     for sigma in (1.0, 4.0):   # sigma 4: radii 3+3+5 = 11 ghost rows per side; 7 bands of 23 rows reach two bands away
