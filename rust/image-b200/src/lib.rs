@@ -1,13 +1,19 @@
 //! `image-b200`: the `image` crate's data-parallel pixel hot path on an NVIDIA B200.
 //!
-//! Same signatures as the reference over `ImageBuffer<P, Vec<S>>` and `DynamicImage`
-//! (`imageops::resize`, `blur`, `blur_advanced`, `fast_blur`, `ImageBuffer::convert`,
-//! `DynamicImage::to_*`, `from_raw_bgra` / `into_raw_bgra`), forwarding to `libb200img`'s C ABI.
+//! Same signatures as the reference over `ImageBuffer<P, Vec<S>>` (`imageops::resize`, `blur`, `blur_advanced`,
+//! `fast_blur`, `thumbnail`, `ImageBuffer::convert`, `from_raw_bgr(a)` / `into_raw_bgr(a)`) in this file and over
+//! `DynamicImage` (`to_*` / `into_*`, `resize*`, `blur*`, `fast_blur`, `thumbnail*`) in `dynimage.rs`, plus the
+//! device-resident batch type `DeviceBatch<P>` in `device.rs`, all forwarding to `libb200img`'s C ABI.
 //! There is no CPU fallback: without a usable GPU every call panics with the library's message.
 //!
 //! NOTE: written in an environment without `rustc`/`cargo`; it mirrors `image_b200/imageops.py`
 //! (which is exercised by the test-suite) line for line but has not itself been compiled.
+pub mod device;
+pub mod dynimage;
 pub mod ffi;
+
+pub use device::DeviceBatch;
+pub use dynimage::DynamicImageB200;
 
 use std::ffi::{c_int, c_void, CStr};
 
@@ -25,14 +31,14 @@ impl B200Subpixel for f32 { const DTYPE: c_int = ffi::F32; }
 /// The reference's literal vertical-accumulator start (`Rgba([1.0; 4])`, sample.rs:547).
 pub const ACC_INIT_REFERENCE: f32 = 1.0;
 
-fn check(rc: c_int) {
+pub(crate) fn check(rc: c_int) {
     if rc == 0 { return; }
     let msg = unsafe { CStr::from_ptr(ffi::b200img_last_error()) }.to_string_lossy().into_owned();
     // -1: the reference panics on this input; -2: ImageError::Limits(DimensionError); -3/-4: no memory / no GPU
     panic!("b200img (status {rc}): {msg}");
 }
 
-fn filter_code(f: FilterType) -> c_int {
+pub(crate) fn filter_code(f: FilterType) -> c_int {
     match f {
         FilterType::Nearest => 0, FilterType::Triangle => 1, FilterType::CatmullRom => 2,
         FilterType::Gaussian => 3, FilterType::Lanczos3 => 4,
@@ -51,7 +57,46 @@ fn packed<I: GenericImageView>(image: &I) -> Vec<<I::Pixel as Pixel>::Subpixel> 
 
 pub mod imageops {
     use super::*;
-    pub use crate::ffi::b200img_gauss_params as GaussianBlurParameters;
+
+    /// `image::imageops::GaussianBlurParameters` (src/imageops/sample.rs:1081-1295): same constructors, same asserts
+    /// (the library validates and the wrapper panics, as the reference does).
+    #[derive(Clone, Copy, Debug, PartialEq)]
+    pub struct GaussianBlurParameters(ffi::b200img_gauss_params);
+    impl GaussianBlurParameters {
+        pub const SMOOTHING_3: GaussianBlurParameters = GaussianBlurParameters(ffi::b200img_gauss_params { x_kernel_size: 3, x_sigma: 0.8, y_kernel_size: 3, y_sigma: 0.8 });
+        pub const SMOOTHING_5: GaussianBlurParameters = GaussianBlurParameters(ffi::b200img_gauss_params { x_kernel_size: 5, x_sigma: 1.1, y_kernel_size: 5, y_sigma: 1.1 });
+        pub const SMOOTHING_7: GaussianBlurParameters = GaussianBlurParameters(ffi::b200img_gauss_params { x_kernel_size: 7, x_sigma: 1.4, y_kernel_size: 7, y_sigma: 1.4 });
+        fn make(f: impl FnOnce(*mut ffi::b200img_gauss_params) -> c_int) -> GaussianBlurParameters {
+            let mut p = ffi::b200img_gauss_params { x_kernel_size: 0, x_sigma: 0.0, y_kernel_size: 0, y_sigma: 0.0 };
+            check(f(&mut p));
+            GaussianBlurParameters(p)
+        }
+        pub fn new_from_radius(radius: f32) -> GaussianBlurParameters { Self::make(|p| unsafe { ffi::b200img_gauss_params_from_radius(radius, p) }) }
+        pub fn new_from_kernel_size(kernel_size: f32) -> GaussianBlurParameters { Self::make(|p| unsafe { ffi::b200img_gauss_params_from_kernel_size(kernel_size, p) }) }
+        pub fn new_anisotropic_kernel_size(x_axis_kernel_size: f32, y_axis_kernel_size: f32) -> GaussianBlurParameters {
+            Self::make(|p| unsafe { ffi::b200img_gauss_params_from_anisotropic(x_axis_kernel_size, y_axis_kernel_size, p) })
+        }
+        pub fn new_from_sigma(sigma: f32) -> GaussianBlurParameters { Self::make(|p| unsafe { ffi::b200img_gauss_params_from_sigma(sigma, p) }) }
+        pub(crate) fn raw(&self) -> ffi::b200img_gauss_params { self.0 }
+    }
+
+    /// `resize_impl`'s control flow around the resampler (src/imageops/resize.rs:27-34, 88-90, 105-218): images with
+    /// a varying alpha channel are premultiplied before and unpremultiplied after any filter but Nearest.
+    pub fn resize_alpha_aware<P: Pixel>(image: &ImageBuffer<P, Vec<P::Subpixel>>, nwidth: u32, nheight: u32, filter: FilterType)
+        -> ImageBuffer<P, Vec<P::Subpixel>>
+    where P::Subpixel: B200Subpixel
+    {
+        let has_alpha = P::CHANNEL_COUNT == 2 || P::CHANNEL_COUNT == 4;
+        if !has_alpha || matches!(filter, FilterType::Nearest) || has_constant_alpha(image) {
+            return resize(image, nwidth, nheight, filter);
+        }
+        let (w, h) = image.dimensions();
+        let mut pre = image.clone();
+        check(unsafe { ffi::b200img_premultiply_alpha(pre.as_mut_ptr() as *mut c_void, w, h, P::CHANNEL_COUNT as c_int, <P::Subpixel as B200Subpixel>::DTYPE) });
+        let mut out = resize(&pre, nwidth, nheight, filter);
+        check(unsafe { ffi::b200img_unpremultiply_alpha(out.as_mut_ptr() as *mut c_void, nwidth, nheight, P::CHANNEL_COUNT as c_int, <P::Subpixel as B200Subpixel>::DTYPE) });
+        out
+    }
 
     /// `image::imageops::resize` (src/imageops/sample.rs:970).
     pub fn resize<I: GenericImageView>(image: &I, nwidth: u32, nheight: u32, filter: FilterType)
@@ -74,16 +119,6 @@ pub mod imageops {
         out
     }
 
-    pub fn params_from_radius(radius: f32) -> GaussianBlurParameters {
-        let mut p = GaussianBlurParameters { x_kernel_size: 0, x_sigma: 0.0, y_kernel_size: 0, y_sigma: 0.0 };
-        check(unsafe { ffi::b200img_gauss_params_from_radius(radius, &mut p) });
-        p
-    }
-    pub fn params_from_sigma(sigma: f32) -> GaussianBlurParameters {
-        let mut p = GaussianBlurParameters { x_kernel_size: 0, x_sigma: 0.0, y_kernel_size: 0, y_sigma: 0.0 };
-        check(unsafe { ffi::b200img_gauss_params_from_sigma(sigma, &mut p) });
-        p
-    }
 
     fn gauss<I: GenericImageView>(image: &I, p: GaussianBlurParameters, path: c_int)
         -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
@@ -93,13 +128,13 @@ pub mod imageops {
         let mut out = ImageBuffer::new(image.width(), image.height());
         check(unsafe { ffi::b200img_gaussian_blur(src.as_ptr() as *const c_void, image.width(), image.height(),
             <I::Pixel as Pixel>::CHANNEL_COUNT as c_int, <<I::Pixel as Pixel>::Subpixel as B200Subpixel>::DTYPE,
-            out.as_mut_ptr() as *mut c_void, &p, path, ffi::FP_FAST) });
+            out.as_mut_ptr() as *mut c_void, &p.raw(), path, ffi::FP_FAST) });
         out
     }
 
     /// `image::imageops::blur` -- `radius`, not sigma, at this revision (sample.rs:1034).
     pub fn blur<I: GenericImageView>(image: &I, radius: f32) -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
-    where <I::Pixel as Pixel>::Subpixel: B200Subpixel { gauss(image, params_from_radius(radius), ffi::BLUR_GENERIC) }
+    where <I::Pixel as Pixel>::Subpixel: B200Subpixel { gauss(image, GaussianBlurParameters::new_from_radius(radius), ffi::BLUR_GENERIC) }
 
     /// `image::imageops::blur_advanced` (sample.rs:1050).
     pub fn blur_advanced<I: GenericImageView>(image: &I, p: GaussianBlurParameters) -> ImageBuffer<I::Pixel, Vec<<I::Pixel as Pixel>::Subpixel>>
@@ -242,7 +277,40 @@ pub fn swizzle_02<S: B200Subpixel>(buf: &mut [S], channels: usize) {
     check(unsafe { ffi::b200img_swizzle_02(buf.as_mut_ptr() as *mut c_void, S::DTYPE, channels as c_int, buf.len()) });
 }
 
-/// Device-resident batch variant: `n` equally shaped images already in device memory.
+/// `ImageBuffer::<Rgb<S>, _>::from_raw_bgr` (src/images/buffer.rs:1551): a BGR buffer becomes an RGB image.
+pub fn from_raw_bgr<S: B200Subpixel>(width: u32, height: u32, mut container: Vec<S>) -> Option<ImageBuffer<image::Rgb<S>, Vec<S>>>
+where image::Rgb<S>: Pixel<Subpixel = S>
+{
+    if (container.len() as u64) < width as u64 * height as u64 * 3 { return None; }
+    swizzle_02(&mut container, 3);
+    ImageBuffer::from_raw(width, height, container)
+}
+/// `into_raw_bgr` (buffer.rs:1558).
+pub fn into_raw_bgr<S: B200Subpixel>(image: ImageBuffer<image::Rgb<S>, Vec<S>>) -> Vec<S>
+where image::Rgb<S>: Pixel<Subpixel = S>
+{
+    let mut raw = image.into_raw();
+    swizzle_02(&mut raw, 3);
+    raw
+}
+/// `ImageBuffer::<Rgba<S>, _>::from_raw_bgra` (buffer.rs:1571).
+pub fn from_raw_bgra<S: B200Subpixel>(width: u32, height: u32, mut container: Vec<S>) -> Option<ImageBuffer<image::Rgba<S>, Vec<S>>>
+where image::Rgba<S>: Pixel<Subpixel = S>
+{
+    if (container.len() as u64) < width as u64 * height as u64 * 4 { return None; }
+    swizzle_02(&mut container, 4);
+    ImageBuffer::from_raw(width, height, container)
+}
+/// `into_raw_bgra` (buffer.rs:1578).
+pub fn into_raw_bgra<S: B200Subpixel>(image: ImageBuffer<image::Rgba<S>, Vec<S>>) -> Vec<S>
+where image::Rgba<S>: Pixel<Subpixel = S>
+{
+    let mut raw = image.into_raw();
+    swizzle_02(&mut raw, 4);
+    raw
+}
+
+/// Device-resident batch on raw pointers (see `DeviceBatch` for the owning type): `n` equally shaped images already in device memory.
 /// # Safety
 /// `d_src` / `d_dst` must be valid device pointers on the current CUDA device; `stream` a valid `cudaStream_t` or null.
 pub unsafe fn resize_batch_dev(d_src: *const c_void, w: u32, h: u32, channels: u32, dtype: c_int, d_dst: *mut c_void,
