@@ -23,8 +23,9 @@ if name in ("k4", "k1", "k5"):
     src = (torch.rand((n, h, w, 4), device=dev, generator=g) * (255 if tdt == torch.uint8 else 1)).to(tdt)
     dst = torch.empty((n, nh, nw, 4), dtype=tdt, device=dev)
     fn = lambda: L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, dt, dst.data_ptr(), 0, nw, nh, n, int(f), 1.0, 0, st))
-elif name in ("gauss65", "gauss21", "gauss65q", "fast"):
-    n = 2
+elif name in ("gauss65", "gauss21", "gauss65q", "fast", "gauss65x8", "fastx8"):
+    n = 8 if name.endswith("x8") else 2
+    name = name[:-2] if name.endswith("x8") else name
     src = torch.randint(0, 256, (n, 2160, 3840, 3), dtype=torch.uint8, device=dev, generator=g)
     dst = torch.empty_like(src)
     if name == "fast":
