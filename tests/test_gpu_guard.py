@@ -1,6 +1,9 @@
 """Out-of-bounds WRITE check for every device entry point: the destination sits between two guard
 bands inside a larger allocation; the bands must come back untouched and the result must equal
-the one computed into a plain buffer.  (compute-sanitizer is not available on the GPU pool.)"""
+the one computed into a plain buffer.  (compute-sanitizer is closed on the GPU pool -- its exact answer is kept in
+profiles/r02_sanitizer_closed.txt -- so this, NaN-filled ghost rows in the band tests and the oracle comparisons of
+every kernel at many ragged shapes stand in for memcheck; the staged / ring buffers of the fused kernels are sized by
+the same host code that the shape tests drive through every tap remainder.)"""
 import ctypes as C
 
 import numpy as np
@@ -68,3 +71,38 @@ def test_guard_bands(cuda, dtype, c):
                 for mode in (L.CAST, L.CONVERT):
                     guarded(cuda, h * w * dc * des, lambda d: lib.b200img_convert_dev(sp, dt, c, d, ddt, dc, h * w, mode, None, st),
                             off if des <= es else 0)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("c", [1, 3, 4])
+def test_guard_bands_fused_kernels_and_bands(cuda, dtype, c):
+    """The kernels added in round 2: the fused Gaussian (forced, also where the library would not pick it), the fused
+    box blur (u8 rows of whole words, several strips and bands) and the row-band entry points of both blurs."""
+    import torch
+    lib = L.lib()
+    rng = np.random.default_rng(300 + c)
+    es = np.dtype(dtype).itemsize
+    dt = DT[np.dtype(dtype)]
+    st = torch.cuda.current_stream().cuda_stream
+    for (h, w) in ((45, 76), (133, 260)):
+        img = rand_image(rng, h, w, c, dtype)
+        src = torch.from_numpy(img).to(cuda)
+        sp = src.data_ptr()
+        n = h * w * c * es
+        for off in (0, es):
+            for sigma in (1.0, 4.0, 10.0):
+                p = GaussianBlurParameters.new_from_sigma(sigma)
+                for path in (L.BLUR_GENERIC, L.BLUR_DYN):
+                    guarded(cuda, n, lambda d: lib.b200img_gaussian_blur_dev(sp, w, h, c, dt, d, C.byref(p.raw), path, L.GAUSS_FUSED, st), off)
+                guarded(cuda, n, lambda d: lib.b200img_fast_blur_dev(sp, w, h, c, dt, d, sigma, st), off)
+            # a band in the middle of the image from a buffer that holds exactly the rows it reads
+            p = GaussianBlurParameters.new_from_sigma(2.0)
+            r0, rows = h // 3, h // 3
+            s0, sn = C.c_uint32(), C.c_uint32()
+            L.check(lib.b200img_gaussian_blur_band_src_rows(h, C.byref(p.raw), r0, rows, C.byref(s0), C.byref(sn)))
+            band = torch.from_numpy(np.ascontiguousarray(img[s0.value:s0.value + sn.value])).to(cuda)
+            guarded(cuda, rows * w * c * es, lambda d: lib.b200img_gaussian_blur_band_dev(band.data_ptr(), s0.value, sn.value, w, h, c, dt, d, r0, rows,
+                                                                                         C.byref(p.raw), L.BLUR_DYN, 0, st), off)
+            L.check(lib.b200img_fast_blur_band_src_rows(h, 2.0, r0, rows, C.byref(s0), C.byref(sn)))
+            band = torch.from_numpy(np.ascontiguousarray(img[s0.value:s0.value + sn.value])).to(cuda)
+            guarded(cuda, rows * w * c * es, lambda d: lib.b200img_fast_blur_band_dev(band.data_ptr(), s0.value, sn.value, w, h, c, dt, d, r0, rows, 2.0, st), off)
