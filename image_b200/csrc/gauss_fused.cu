@@ -53,6 +53,7 @@ struct FusedArgs {
     int win_chunks;    // ring chunks one output chunk reads (its window rounded up to whole chunks)
     int dbg;           // timing experiments only (B200IMG_GF_DBG): 1 = no staging work, 2 = no output stores, 4 = no ring stores, 8 = no multiply-adds
     int in_pitch;      // floats per staged row (odd)
+    int raw_pitch;     // u8 only: words per row of the raw-byte buffers in front of the f32 staging (0 = not used)
     int sp;            // staged pixels per row
 };
 
@@ -254,6 +255,111 @@ gauss_fused_kernel(const __grid_constant__ FusedArgs a, const __grid_constant__ 
         constexpr int EPW = 4 / (int)sizeof(In);                            // subpixels per 32-bit word
         constexpr int PF_W = sizeof(In) == 1 ? 4 : 8;                       // words per lane per row held in registers
         const int row_elems = a.sp * C;
+        if constexpr (sizeof(In) == 1) {
+            if (a.raw_pitch) {
+                // ---- u8, word-aligned rows (the host checked): raw bytes first, conversion second ----
+                // The warp's 8 rows of chunk g + 1 are on their way into a raw-byte buffer (cp.async, no registers
+                // held) while its rows of chunk g are converted from the other raw buffer into the f32 staging
+                // buffer: a chunk's DRAM latency hides behind the previous chunk's conversion, and the whole path is
+                // two small rolled loops (the register-prefetch path below is 13 KB of straight-line code that the
+                // staging warp drags through the sub-partition's instruction cache every chunk).
+                uint32_t *raw0 = reinterpret_cast<uint32_t *>(stage0 + 2 * stage_floats);   // 2 x [32][raw_pitch] words
+                const uint32_t raw_words = (uint32_t)GF_CH * a.raw_pitch;
+                struct Cursor {
+                    long long u_next;   // first unit after this segment
+                    Segment sg;
+                    int i;              // row chunk within the segment
+                    const uint8_t *src; // image base
+                    int lo_px, e_off, n_in, phase, words;
+                    bool valid;
+                };
+                auto open_segment = [&](long long u, Cursor &c) {
+                    c.valid = u < u_end;
+                    if (!c.valid) return;
+                    c.u_next = segment_at(u, c.sg);
+                    c.i = 0;
+                    c.src = reinterpret_cast<const uint8_t *>(a.src) + (size_t)c.sg.img * a.src_img_stride;
+                    const int xs = c.sg.x0 - a.half_r;
+                    c.lo_px = max(xs, 0);
+                    const int hi_px = min(xs + a.sp, (int)a.W);
+                    c.e_off = (c.lo_px - xs) * C;
+                    c.n_in = (hi_px - c.lo_px) * C;
+                    c.phase = (int)(((size_t)c.lo_px * C) & 3);
+                    c.words = (c.phase + c.n_in + 3) >> 2;
+                };
+                auto advance = [&](Cursor &c) {
+                    if (++c.i >= c.sg.ni) open_segment(c.u_next, c);
+                };
+                auto row_ptr = [&](const Cursor &c, int r) -> const uint8_t * {
+                    int y = min(max(c.sg.q0 + c.i * GF_CH + r, 0), (int)a.H - 1);
+                    y = min(max(y, (int)a.src_row0), (int)(a.src_row0 + a.src_rows_buf) - 1);
+                    return c.src + (size_t)(y - (int)a.src_row0) * g_pitch + ((size_t)c.lo_px * C - c.phase);
+                };
+                auto issue_copies = [&](const Cursor &c, uint32_t *raw) {
+#pragma unroll 2
+                    for (int k = 0; k < PF_ROWS; ++k) {
+                        const int r = pw + k * GF_PWARPS;
+                        const uint32_t *gw = reinterpret_cast<const uint32_t *>(row_ptr(c, r)) + lane;
+                        uint32_t d = smem_u32(raw + r * a.raw_pitch + lane);
+                        for (int wi = lane; wi < c.words; wi += 32, gw += 32, d += 128)
+                            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gw) : "memory");
+                    }
+                };
+                Cursor cur, nxt;
+                open_segment(u_begin, cur);
+                if (cur.valid) issue_copies(cur, raw0);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                const int rot = lane >> 3;  // lanes 8 apart start on different bytes, so the four stores of a word hit 32 different banks
+                for (uint32_t g = 0; cur.valid; ++g) {
+                    nxt = cur;
+                    advance(nxt);
+                    if (nxt.valid && !(a.dbg & 1)) issue_copies(nxt, raw0 + ((g + 1) & 1) * raw_words);
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                    asm volatile("cp.async.wait_group 1;" ::: "memory");   // this chunk's bytes have landed (each lane converts the words it copied)
+                    mbar_wait_parked(&bar_empty[g & 1], ((g >> 1) & 1) ^ 1, hint);  // the row pass two chunks back has left the f32 buffer
+                    float *s_in = stage0 + (size_t)(g & 1) * stage_floats;
+                    if (!(a.dbg & 1)) {
+                        const uint32_t *raw = raw0 + (g & 1) * raw_words;
+                        const int first_full = cur.phase ? 1 : 0, last_full = (cur.phase + cur.n_in) >> 2;  // whole words: [first_full, last_full)
+#pragma unroll 1
+                        for (int k = 0; k < PF_ROWS; ++k) {
+                            const int r = pw + k * GF_PWARPS;
+                            const uint32_t *rw = raw + r * a.raw_pitch;
+                            float *sd = s_in + r * a.in_pitch + cur.e_off - cur.phase;   // word wi starts at sd[wi * 4]
+#pragma unroll 2
+                            for (int wi = lane; wi < cur.words; wi += 32) {
+                                const uint32_t w = rw[wi];
+                                if (wi >= first_full && wi < last_full) {
+#pragma unroll
+                                    for (int jj = 0; jj < 4; ++jj) {
+                                        const int j = (jj + rot) & 3;
+                                        sd[wi * 4 + j] = byte_to_f32(w, j);
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j) {
+                                        const int e = wi * 4 + j - cur.phase;
+                                        if (e >= 0 && e < cur.n_in) sd[wi * 4 + j] = byte_to_f32(w, j);
+                                    }
+                                }
+                            }
+                        }
+                        if (cur.n_in < row_elems) {  // an edge strip: replicate the span's first / last pixel outwards
+                            __syncwarp();
+                            for (int r = pw; r < GF_CH; r += GF_PWARPS) {
+                                float *sr = s_in + r * a.in_pitch;
+                                for (int e = lane; e < cur.e_off; e += 32) sr[e] = sr[cur.e_off + e % C];
+                                const int right0 = cur.e_off + cur.n_in;
+                                for (int e = right0 + lane; e < row_elems; e += 32) sr[e] = sr[right0 - C + (e - right0) % C];
+                            }
+                        }
+                    }
+                    mbar_arrive(&bar_full[g & 1]);
+                    cur = nxt;
+                }
+                return;
+            }
+        }
         uint32_t g = 0;  // row chunks staged so far
         Segment sg;
         for (long long u = u_begin; u < u_end;) {
@@ -512,14 +618,28 @@ int gauss_fused_run(const T *src, T *dst, uint32_t w, uint32_t h, int C, uint32_
     a.in_pitch = (a.sp * C + 1) | 1;
     // ring: the window plus as many spare chunks (up to two) as shared memory has room for -- the row warps may
     // run that far ahead of the column warps; at least one, or the two groups would alternate instead of overlap
+    // (two against one: 1.190 against 1.194 ms on the bench shape).  Where the raw-byte staging buffers are used (see
+    // the staging warps) they take the second spare chunk's room.
     const size_t stage_bytes = 2 * (size_t)GF_CH * a.in_pitch * sizeof(float), chunk_bytes = (size_t)GF_CH * RP * sizeof(float);
     const size_t room = ctx->smem_optin > 1024 ? ctx->smem_optin - 1024 : 0;  // static shared memory: the barriers
+    a.raw_pitch = 0;
+    size_t raw_bytes = 0;
+    // Measured on B200 (8 x 4K, sigma 10): Rgba8 1.59 ms with the raw buffers against 1.72 without (113 words a row leave the
+    // register path's fourth load slot half empty); Rgb8 1.26 against 1.18, Luma8 0.43 against 0.42 -- so four channels only.
+    const char *raw_env = getenv("B200IMG_GF_RAW");  // tuning aid: 0 / 1 force it off / on
+    const bool want_raw = raw_env ? atoi(raw_env) != 0 : C == 4;
+    if (want_raw && std::is_same<T, uint8_t>::value && ((size_t)w * C) % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0 &&
+        ((size_t)w * src_rows_buf * C) % 4 == 0) {
+        a.raw_pitch = (a.sp * C + 3 + 3) / 4;   // the widest span plus its byte phase, in words
+        raw_bytes = 2 * (size_t)GF_CH * a.raw_pitch * 4;
+        if (stage_bytes + raw_bytes + (size_t)(a.win_chunks + 1) * chunk_bytes > room) { a.raw_pitch = 0; raw_bytes = 0; }
+    }
     int spare = 2;
     if (const char *e = getenv("B200IMG_GF_SPARE")) spare = std::max(1, std::min(2, atoi(e)));  // tuning aid
-    while (spare > 0 && stage_bytes + (size_t)(a.win_chunks + spare) * chunk_bytes > room) --spare;
+    while (spare > 0 && stage_bytes + raw_bytes + (size_t)(a.win_chunks + spare) * chunk_bytes > room) --spare;
     if (spare == 0 || a.win_chunks + spare > GF_MAX_SLOTS) return 1;
     a.RR = (a.win_chunks + spare) * GF_CH;
-    const size_t smem = stage_bytes + (size_t)a.RR * RP * sizeof(float);
+    const size_t smem = stage_bytes + raw_bytes + (size_t)a.RR * RP * sizeof(float);
     if (dst_rows == 0 || n_images == 0) return 0;
 
     a.src = src; a.dst = dst; a.W = w; a.H = h;

@@ -51,11 +51,13 @@ def test_gaussian_fused_kernel_shapes(cuda, dtype, c, monkeypatch):
     img = rand_image(rng, 150, 333 if c < 3 else 131, c, dtype)
     for sigma in (0.5, 0.8, 1.2, 1.5, 2.0, 3.5, 10.0, 15.5):   # 3, 5, 5, 7, 11, 21, 65, 101 taps
         _gauss_check(img, GaussianBlurParameters.new_from_sigma(sigma), cuda)
-    for ctas in ("1", "7", "1000"):
+    for ctas, raw in (("1", "1"), ("7", "0"), ("1000", "1")):   # forced CTA counts; the raw-byte staging path (u8) on and off
         monkeypatch.setenv("B200IMG_GF_CTAS", ctas)
+        monkeypatch.setenv("B200IMG_GF_RAW", raw)
         _gauss_check(img, GaussianBlurParameters.new_from_sigma(4.0), cuda)
         _gauss_check(rand_image(rng, 37, 21, c, dtype), GaussianBlurParameters.new_anisotropic_kernel_size(15.0, 41.0), cuda)
     monkeypatch.delenv("B200IMG_GF_CTAS")
+    monkeypatch.delenv("B200IMG_GF_RAW")
     _gauss_check(rand_image(rng, 3, 500, c, dtype), GaussianBlurParameters.new_from_sigma(3.0), cuda)
     _gauss_check(rand_image(rng, 300, 2, c, dtype), GaussianBlurParameters.new_from_sigma(3.0), cuda)
 
