@@ -15,6 +15,7 @@ U8, U16, F32 = 0, 1, 2
 NEAREST, TRIANGLE, CATMULLROM, GAUSSIAN, LANCZOS3 = range(5)
 FP_FAST, FP_STRICT, FP_FUSED_MAC, RESIZE_UNFUSED, RESIZE_TILED, THUMBNAIL_PER_PIXEL = 0, 1, 2, 256, 512, 1024
 GAUSS_TWO_KERNELS, GAUSS_FUSED = 2048, 4096
+RESIZE_GENERAL = 8192
 BLUR_GENERIC, BLUR_DYN = 0, 1
 CAST, CONVERT = 0, 1
 OK, ERR_BAD_ARG, ERR_DIMENSION, ERR_OOM, ERR_CUDA, ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5

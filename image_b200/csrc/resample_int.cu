@@ -1,0 +1,452 @@
+// resample_int.cu -- the resampler for downscales by an EVEN INTEGER ratio (2x, 4x, ...) of u8 images
+// under B200IMG_FP_FAST: thumbnails and mip levels, BASELINE configs 0 (1080p -> 540p, Lanczos3) and 3
+// (1024^2 -> 256^2, CatmullRom).
+//
+// For such a ratio R every output sample away from the borders has the SAME window shape: its window
+// starts at source sample R * o + L0 and has NT = 2 * support * R taps whose weights depend on the tap
+// index only (vertical_sample / horizontal_sample, src/imageops/sample.rs:494-562, 217-340: the centre
+// (o + 0.5) * R lies on the same sub-sample phase for every o).  So both passes are strided
+// convolutions with ONE weight vector, and everything the general streaming kernel
+// (resample_stream.cu) spends on per-row weight tables in shared memory, accumulator-slot bookkeeping
+// and register shifting goes away:
+//   vertical:   a thread owns a 32-bit word column of the source strip (4 subpixels) and streams down
+//               the rows once.  A = NT / R output rows are open at any time; with the row loop
+//               unrolled over one period of A * R rows, which accumulator a row feeds and with which
+//               tap is known at compile time: weights come from the kernel-parameter bank as
+//               uniform operands of FFMA2, closed rows leave from a fixed accumulator.
+//   horizontal: every HR finished rows, lane = row, a warp item = two 8-pixel blocks of one channel:
+//               16 outputs per thread from ONE walk over the R * 7 + NT samples their windows span
+//               (each sample is loaded once and feeds up to A outputs), weights again uniform.
+// Borders: the reference clips a window at the image edge and renormalises the remaining weights.
+// Here samples outside the image contribute zero and the result is multiplied by
+// 1 / (sum of the weights that stayed inside) -- the same numbers up to f32 rounding, which the FAST
+// contract (+-1 LSB) covers; STRICT runs never come here.  The accumulator's start value acc_init
+// (sample.rs:547) is added once after the vertical pass (the horizontal weights sum to one).
+#include "common.cuh"
+#include "host_tables.h"
+#include "packed.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+namespace {
+
+constexpr int RI_THREADS = 320;  // word columns per strip, at most (the block is as wide as the strip needs)
+constexpr int RI_MAX_TAPS = 24;
+
+struct IntArgs {
+    const void *src;
+    void *dst;
+    size_t src_img_stride, dst_img_stride;  // bytes
+    uint32_t w, h, nw, nh;
+    uint32_t src_row0, dst_row0, dst_rows;  // the source buffer's first row; destination rows to produce
+    int L0v, L0h;       // the window of output o starts at source sample R * o + L0 (before clipping)
+    int TW, BAND;       // output pixels per strip (multiple of 16); output rows per band (multiple of HR)
+    int tmp_pitch;      // floats per ring row (1 mod 32: lane = row reads hit 32 banks)
+    int out_pitch;      // bytes per staged output row (4 * odd)
+    float acc_init;
+    f32x2 wv[RI_MAX_TAPS], wh[RI_MAX_TAPS];  // (w, w) pairs
+};
+
+__device__ __forceinline__ float lo_of(f32x2 v) { float a, b; unpack2(v, a, b); return a; }
+
+// The weight vectors are symmetric (the host checked): tap k and tap NT - 1 - k share one entry, so that the NT / 2 distinct
+// (w, w) pairs of an axis stay resident in uniform registers.
+#define RI_SYM(w, k) ((w)[(k) < NT / 2 ? (k) : NT - 1 - (k)])
+
+// 1 / (sum of the taps of a window starting at `first` that fall inside [0, len)).  Only windows that the image's edge clips
+// come here (a few rows and columns per image): kept out of line so that the unrolled passes stay small.
+template <int NT>
+__device__ __noinline__ float border_scale(const f32x2 *w, int first, int len) {
+    const int k0 = max(0, -first), k1 = min(NT, len - first);
+    float s = 0.0f;
+#pragma unroll 1
+    for (int k = k0; k < k1; ++k) s += lo_of(RI_SYM(w, k));
+    return 1.0f / s;
+}
+
+// (v + 0.5) as u8 of four values (NearestFrom<f32> for u8, src/primitive_sealed.rs:110-120) packed into one word, on the FMA
+// pipe only: clamp, then an addition to 2^23 that rounds toward zero leaves floor(v + 0.5) in the low mantissa byte.
+__device__ __forceinline__ uint32_t pack_u8x4(float r, float g, float b, float al) {
+    auto q = [](float v) -> uint32_t {
+        const float t = fminf(fmaxf(__fadd_rn(v, 0.5f), 0.0f), 255.5f);
+        return __float_as_uint(__fadd_rz(t, 8388608.0f));
+    };
+    const uint32_t rg = __byte_perm(q(r), q(g), 0x0040), ba = __byte_perm(q(b), q(al), 0x0040);
+    return __byte_perm(rg, ba, 0x5410);
+}
+
+template <int C, int R, int A>
+__global__ void __launch_bounds__(RI_THREADS)
+resize_int_kernel(const __grid_constant__ IntArgs a) {
+    constexpr int NT = A * R;            // taps
+    constexpr int P = A * R;             // rows of one period of the vertical pass
+    constexpr int HR = A == 6 ? 30 : 32; // ring rows = output rows per horizontal phase (a multiple of A)
+    constexpr int PH = HR / A;           // periods per horizontal phase
+    constexpr int D = P <= 16 ? P : P / 2;  // source rows in flight per thread (divides P: the row buffer is indexed statically)
+    constexpr int SPAN = R * 7 + NT;     // samples the windows of 8 consecutive outputs span
+    constexpr bool PX = C == 4;          // a source word is one pixel: the ring holds float4 pixels (128-bit stores and loads)
+    constexpr int PAD = PX ? 0 : 3;      // ring columns in front of the strip's first sample (the first word may start before it)
+    static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *s_tmp = reinterpret_cast<float *>(smem);                                    // [HR][tmp_pitch]
+    uint8_t *s_out = reinterpret_cast<uint8_t *>(s_tmp + (size_t)HR * a.tmp_pitch);     // [HR][out_pitch]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
+    const unsigned img = blockIdx.z;
+    const int ox0 = blockIdx.x * a.TW;
+    const int tw = min(a.TW, (int)a.nw - ox0);
+    const int oyA = (int)a.dst_row0 + blockIdx.y * a.BAND;
+    const int nout = min(a.BAND, (int)(a.dst_row0 + a.dst_rows) - oyA);
+    if (nout <= 0) return;
+
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(a.src) + (size_t)img * a.src_img_stride;
+    uint8_t *dst = reinterpret_cast<uint8_t *>(a.dst) + (size_t)img * a.dst_img_stride;
+    const size_t gp = (size_t)a.w * C;           // source row pitch in bytes (a multiple of 4: the host checked)
+    const int p0 = R * ox0 + a.L0h;              // source pixel of ring column 0 (may be negative)
+    const int p1 = R * (ox0 + tw - 1) + a.L0h + NT;
+    const int b0 = (max(p0, 0) * C) & ~3;        // first source byte of the strip's words
+    const int b1 = min((min(p1, (int)a.w) * C + 3) & ~3, (int)gp);
+    const int words = (b1 - b0) >> 2;            // <= blockDim.x (the host's choice of TW)
+    const bool active = tid < words;
+    const int col0 = b0 + 4 * tid - p0 * C + PAD;  // ring column of this thread's first subpixel (>= 0: b0 was rounded down by < 4)
+    const bool edge = p0 < 0 || p1 > (int)a.w;   // only strips that touch the image's left / right edge have clipped windows
+
+    // a ring of zeros: the columns of samples outside the image are never written and must contribute nothing
+    for (int i = tid; i < HR * a.tmp_pitch; i += nthreads) s_tmp[i] = 0.0f;
+    __syncthreads();
+
+    // ---- vertical stream: row u of the stream is source row jbase + u, one virtual output in front of the band (so that
+    // period m completes exactly the outputs (m - 1) A .. m A - 1); rows that no output of this band taps, and rows outside
+    // the image, count as zero.  Which rows those are is the same for the whole CTA; threads beyond the strip's last word
+    // follow word 0 (their sums are never stored). ----
+    const int jbase = R * oyA + a.L0v - R;
+    const int ulo = max(R * oyA + a.L0v, 0) - jbase;
+    const unsigned ulen = (unsigned)(min((int)a.h, R * (oyA + nout - 1) + a.L0v + NT) - jbase - ulo);
+    const uint8_t *gptr = src + b0 + 4 * (active ? tid : 0) + ((ptrdiff_t)jbase - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
+    int unext = 0;  // the stream row gptr points at
+    auto load_next = [&]() -> uint32_t {
+        uint32_t v = 0u;
+        if ((unsigned)(unext - ulo) < ulen) v = __ldg(reinterpret_cast<const uint32_t *>(gptr));
+        gptr += gp;
+        ++unext;
+        return v;
+    };
+    f32x2 lo[A], hi[A];
+#pragma unroll
+    for (int s = 0; s < A; ++s) { lo[s] = 0ull; hi[s] = 0ull; }
+    const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+    const f32x2 init2 = pack2(a.acc_init, a.acc_init);
+    // ring stores of the generic layout: lanes 8 apart start on different subpixels of their word, so a store hits 32 banks
+    const int rot = lane >> 3;
+    const int ro0 = rot & 3, ro1 = (rot + 1) & 3, ro2 = (rot + 2) & 3, ro3 = (rot + 3) & 3;
+    float *const tflush0 = s_tmp + col0;
+    float *tflush = tflush0;
+    const int periods = (nout + A - 1) / A + 1;
+    const int rl = min(lane, HR - 1);  // lanes beyond the ring's last row recompute it (and store nothing)
+
+    auto horizontal = [&](int n0, int rows_g) {
+        // destination rows oyA + n0 .. + rows_g; their intermediates are ring rows 0 .. rows_g
+        __syncthreads();
+        const int nb = a.TW >> 3;                 // 8-pixel blocks per strip (even)
+        if constexpr (PX) {
+            // a warp item = one block of 8 pixels, all four channels: a 128-bit load per sample, (r, g) and (b, a) as packed pairs
+            const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_tmp + (size_t)rl * a.tmp_pitch);
+            uint32_t *orow = reinterpret_cast<uint32_t *>(s_out + (size_t)rl * a.out_pitch);
+            for (int item = warp; item < nb; item += nwarps) {
+                const int xa = item * 8;
+                const ulonglong2 *t = trow + R * xa;
+                f32x2 acc[8][2];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { acc[i][0] = 0ull; acc[i][1] = 0ull; }
+#pragma unroll
+                for (int e = 0; e < SPAN; ++e) {
+                    const ulonglong2 px = t[e];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int k = e - R * i;
+                        if (k >= 0 && k < NT) {
+                            acc[i][0] = fma2(px.x, RI_SYM(a.wh, k), acc[i][0]);
+                            acc[i][1] = fma2(px.y, RI_SYM(a.wh, k), acc[i][1]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float r, g, b, al;
+                    unpack2(acc[i][0], r, g);
+                    unpack2(acc[i][1], b, al);
+                    if (edge) {
+                        const int first = R * (ox0 + xa + i) + a.L0h;
+                        if (first < 0 || first + NT > (int)a.w) {
+                            const float hs = border_scale<NT>(a.wh, first, (int)a.w);
+                            r *= hs; g *= hs; b *= hs; al *= hs;
+                        }
+                    }
+                    if (lane < rows_g && xa + i < tw) orow[xa + i] = pack_u8x4(r, g, b, al);
+                }
+            }
+        } else {
+            // a warp item = two blocks of 8 pixels, one channel: the two blocks' samples as packed pairs
+            const int pairs = (nb >> 1) * C;
+            const float *trow = s_tmp + (size_t)rl * a.tmp_pitch + PAD;
+            for (int item = warp; item < pairs; item += nwarps) {
+                const int pb = item / C, c = item - pb * C;
+                const int xa = pb * 8, xb = (pb + (nb >> 1)) * 8;   // first output pixel of block A / block B (strip-local)
+                const float *ta = trow + (R * xa) * C + c, *tb = trow + (R * xb) * C + c;
+                f32x2 acc[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc[i] = 0ull;
+#pragma unroll
+                for (int e = 0; e < SPAN; ++e) {
+                    const f32x2 x = pack2(ta[e * C], tb[e * C]);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int k = e - R * i;
+                        if (k >= 0 && k < NT) acc[i] = fma2(x, RI_SYM(a.wh, k), acc[i]);
+                    }
+                }
+                uint8_t *oa = s_out + (size_t)rl * a.out_pitch + xa * C + c, *ob = s_out + (size_t)rl * a.out_pitch + xb * C + c;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float va, vb;
+                    unpack2(acc[i], va, vb);
+                    if (edge) {
+                        const int fa = R * (ox0 + xa + i) + a.L0h, fb = R * (ox0 + xb + i) + a.L0h;
+                        if (fa < 0 || fa + NT > (int)a.w) va *= border_scale<NT>(a.wh, fa, (int)a.w);
+                        if (fb < 0 || fb + NT > (int)a.w) vb *= border_scale<NT>(a.wh, fb, (int)a.w);
+                    }
+                    if (lane < rows_g && xa + i < tw) oa[i * C] = Px<uint8_t>::clamp_nearest(va);
+                    if (lane < rows_g && xb + i < tw) ob[i * C] = Px<uint8_t>::clamp_nearest(vb);
+                }
+            }
+        }
+        __syncthreads();
+        const size_t d_pitch = (size_t)a.nw * C;
+        const int sub = tw * C;
+        for (int rr = warp; rr < rows_g; rr += nwarps) {
+            uint8_t *g = dst + (size_t)(oyA + n0 + rr - (int)a.dst_row0) * d_pitch + (size_t)ox0 * C;
+            const uint8_t *sr = s_out + (size_t)rr * a.out_pitch;
+            if ((sub & 3) == 0 && (reinterpret_cast<uintptr_t>(g) & 3) == 0) {
+                for (int v = lane; v < (sub >> 2); v += 32) reinterpret_cast<uint32_t *>(g)[v] = reinterpret_cast<const uint32_t *>(sr)[v];
+            } else {
+                for (int v = lane; v < sub; v += 32) g[v] = sr[v];
+            }
+        }
+        tflush = tflush0;
+    };
+
+    uint32_t buf[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) buf[k] = load_next();
+    for (int m = 0; m < periods; ++m) {
+#pragma unroll
+        for (int q = 0; q < P; ++q) {   // q is a compile-time constant after unrolling
+            float f[4];
+            Word<uint8_t>::biased(buf[q % D], f);
+            buf[q % D] = load_next();
+            const f32x2 f01 = add2(pack2(f[0], f[1]), bias2), f23 = add2(pack2(f[2], f[3]), bias2);
+            const int fq = q / R, qr = q % R;
+#pragma unroll
+            for (int aa = 0; aa < A; ++aa) {
+                const int slot = ((fq - aa) % A + A) % A, tap = qr + R * aa;
+                lo[slot] = fma2(f01, RI_SYM(a.wv, tap), lo[slot]);
+                hi[slot] = fma2(f23, RI_SYM(a.wv, tap), hi[slot]);
+            }
+            if (qr == R - 1) {   // an output row is complete: n = (m - 1) A + fq, in accumulator (fq + 1) mod A
+                const int fs = (fq + 1) % A;
+                const int n = (m - 1) * A + fq;
+                if (n >= 0 && n < nout) {
+                    float vs = 1.0f;
+                    const int first = R * (oyA + n) + a.L0v;
+                    if (first < 0 || first + NT > (int)a.h) vs = border_scale<NT>(a.wv, first, (int)a.h);
+                    const f32x2 vs2 = pack2(vs, vs);
+                    const f32x2 x = fma2(lo[fs], vs2, init2), y = fma2(hi[fs], vs2, init2);
+                    if (active) {
+                        if constexpr (PX) {
+                            *reinterpret_cast<ulonglong2 *>(tflush) = make_ulonglong2(x, y);
+                        } else {
+                            float v0, v1, v2, v3;
+                            unpack2(x, v0, v1);
+                            unpack2(y, v2, v3);
+                            // rotate the four values by `rot` so that store jj writes subpixel (jj + rot) & 3
+                            const float r0 = (rot & 1) ? v1 : v0, r1 = (rot & 1) ? v2 : v1, r2 = (rot & 1) ? v3 : v2, r3 = (rot & 1) ? v0 : v3;
+                            const float t0 = (rot & 2) ? r2 : r0, t1 = (rot & 2) ? r3 : r1, t2 = (rot & 2) ? r0 : r2, t3 = (rot & 2) ? r1 : r3;
+                            tflush[ro0] = t0;
+                            tflush[ro1] = t1;
+                            tflush[ro2] = t2;
+                            tflush[ro3] = t3;
+                        }
+                    }
+                    tflush += a.tmp_pitch;
+                }
+                lo[fs] = 0ull;
+                hi[fs] = 0ull;
+            }
+        }
+        // periods 1 .. m have completed outputs 0 .. m A - 1: a horizontal phase every PH periods and at the band's end
+        const int done = min(m * A, nout);
+        if (m >= 1 && ((m % PH) == 0 || done == nout)) {
+            const int n0 = (done - 1) / HR * HR;
+            horizontal(n0, done - n0);
+            if (done == nout) break;
+        }
+    }
+}
+
+#undef RI_SYM
+
+// The window rule of one axis: every output o of [o0, o1) must tap exactly the samples of [R o + L0, R o + L0 + NT) that lie
+// inside the image, whole windows with bitwise the weights of `wmid`.
+bool axis_is_uniform(const AxisTable &t, int len, int R, int NT, int L0, uint32_t o0, uint32_t o1, const float *wmid) {
+    for (uint32_t o = o0; o < o1; ++o) {
+        const int first = R * (int)o + L0, l = std::max(first, 0), r = std::min(first + NT, len);
+        if (t.left[o] != l || t.count[o] != r - l) return false;
+        if (r - l == NT && std::memcmp(&t.w[(size_t)o * t.stride], wmid, sizeof(float) * NT) != 0) return false;
+    }
+    return true;
+}
+
+int round_up_i(int v, int m) { return (v + m - 1) / m * m; }
+
+struct IntGeo {
+    int TW = 0, threads = 0, strips = 0, tmp_pitch = 0, out_pitch = 0;
+    size_t smem = 0;
+};
+
+IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, int HR) {
+    IntGeo g;
+    g.TW = TW;
+    g.strips = (int)((nw + TW - 1) / TW);
+    int words = 0;
+    for (int s = 0; s < g.strips; ++s) {
+        const int ox0 = s * TW, tw = std::min(TW, (int)nw - ox0);
+        const int p0 = R * ox0 + L0h, p1 = R * (ox0 + tw - 1) + L0h + NT;
+        const int b0 = (std::max(p0, 0) * C) & ~3, b1 = std::min((std::min(p1, (int)w) * C + 3) & ~3, (int)w * C);
+        words = std::max(words, (b1 - b0) / 4);
+    }
+    g.threads = round_up_i(words, 32);
+    int tp;
+    if (C == 4) {  // float4 pixels: an odd number of pixels per row, so that the 128-bit loads of 8 rows hit 8 bank groups
+        const int px = R * (TW - 1) + NT;
+        tp = 4 * (px | 1);
+    } else {
+        tp = 3 + (R * (TW - 1) + NT) * C + 3;
+        tp = round_up_i(tp - 1, 32) + 1;  // 1 mod 32
+    }
+    g.tmp_pitch = tp;
+    int op = round_up_i(TW * C, 4);
+    if ((op / 4) % 2 == 0) op += 4;
+    g.out_pitch = op;
+    g.smem = (size_t)HR * tp * 4 + (size_t)HR * op;
+    return g;
+}
+
+template <int C, int R, int A>
+int launch_ra(const IntArgs &a, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+    auto k = resize_int_kernel<C, R, A>;
+    B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, threads, smem, st>>>(a);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
+template <int C, int R>
+int launch_r(const IntArgs &a, int A, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+    switch (A) {
+        case 2: return launch_ra<C, R, 2>(a, grid, threads, smem, st);
+        case 4: return launch_ra<C, R, 4>(a, grid, threads, smem, st);
+        default: return launch_ra<C, R, 6>(a, grid, threads, smem, st);
+    }
+}
+
+template <int C>
+int launch_c(const IntArgs &a, int R, int A, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+    return R == 2 ? launch_r<C, 2>(a, A, grid, threads, smem, st) : launch_r<C, 4>(a, A, grid, threads, smem, st);
+}
+
+int env_int(const char *name, int dflt) {
+    const char *e = std::getenv(name);
+    return e && *e ? std::atoi(e) : dflt;
+}
+
+}  // namespace
+
+// Returns 1 if this kernel took the job (and launched it), 0 if it does not apply, < 0 on error.
+int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                   size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
+                   const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st) {
+    if (dtype != B200IMG_U8) return 0;
+    if (nw == 0 || nh == 0 || w % nw != 0 || h % nh != 0 || w / nw != h / nh) return 0;
+    const int R = (int)(w / nw);
+    if (R != 2 && R != 4) return 0;
+    const size_t gp = (size_t)w * C;
+    if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
+    if ((uint64_t)w * C > (1u << 30) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
+    const int NT = vt.max_count;
+    if (NT != ht.max_count || NT % R != 0 || NT > RI_MAX_TAPS) return 0;
+    const int A = NT / R;
+    if (A != 2 && A != 4 && A != 6) return 0;
+    // a whole window in the middle of each axis gives the rule and the weights
+    const uint32_t vm = nh / 2, hm = nw / 2;
+    if (vt.count[vm] != NT || ht.count[hm] != NT) return 0;
+    const int L0v = vt.left[vm] - R * (int)vm, L0h = ht.left[hm] - R * (int)hm;
+    const float *wvm = &vt.w[(size_t)vm * vt.stride], *whm = &ht.w[(size_t)hm * ht.stride];
+    for (int k = 0; k < NT / 2; ++k)  // the kernel keeps half of each (symmetric) weight vector
+        if (std::memcmp(&wvm[k], &wvm[NT - 1 - k], 4) != 0 || std::memcmp(&whm[k], &whm[NT - 1 - k], 4) != 0) return 0;
+    if (!axis_is_uniform(vt, (int)h, R, NT, L0v, dst_row0, dst_row0 + dst_rows, wvm)) return 0;
+    if (!axis_is_uniform(ht, (int)w, R, NT, L0h, 0, nw, whm)) return 0;
+
+    const int HR = A == 6 ? 30 : 32;
+    // strip width: the fewest thread columns over the image's width among the widths that leave room for two CTAs per SM
+    IntGeo best;
+    const int forced_tw = env_int("B200IMG_RI_TW", 0);
+    for (int pass = 0; pass < 2 && best.TW == 0; ++pass) {
+        const size_t cap = pass == 0 ? (size_t)(233472 - 2048) / 2 : ctx->smem_optin;
+        for (int TW = 16; TW <= 256; TW += 16) {
+            if (forced_tw && TW != forced_tw) continue;
+            const IntGeo g = int_geo(TW, w, nw, C, R, NT, L0h, HR);
+            if (g.threads > RI_THREADS || g.smem > std::min(cap, ctx->smem_optin)) continue;
+            if (best.TW == 0 || (int64_t)g.threads * g.strips < (int64_t)best.threads * best.strips ||
+                ((int64_t)g.threads * g.strips == (int64_t)best.threads * best.strips && TW > best.TW))
+                best = g;
+        }
+    }
+    if (best.TW == 0) return 0;
+    const int ctas_per_sm = std::max<int>(1, std::min<size_t>(2048 / best.threads, (233472 - 1024) / (best.smem + 1024)));
+    int BAND = 4 * HR;
+    const int forced_band = env_int("B200IMG_RI_BAND", 0);
+    if (forced_band > 0) BAND = round_up_i(forced_band, HR);
+    else
+        while (BAND > HR && (uint64_t)best.strips * ((dst_rows + BAND - 1) / BAND) * n_images < (uint64_t)ctx->sm_count * ctas_per_sm * 3) BAND -= HR;
+    const int bands = (int)((dst_rows + BAND - 1) / BAND);
+    if (bands > 65535 || n_images > 65535) return 0;
+    if ((uint64_t)best.strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;  // a small single image: the tile kernels spread it better
+
+    IntArgs a;
+    a.src = src; a.dst = dst; a.src_img_stride = src_img_stride; a.dst_img_stride = dst_img_stride;
+    a.w = w; a.h = h; a.nw = nw; a.nh = nh; a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
+    a.L0v = L0v; a.L0h = L0h; a.TW = best.TW; a.BAND = BAND; a.tmp_pitch = best.tmp_pitch; a.out_pitch = best.out_pitch;
+    a.acc_init = acc_init;
+    for (int k = 0; k < RI_MAX_TAPS; ++k) {
+        const float v = k < NT ? wvm[k] : 0.0f, hh = k < NT ? whm[k] : 0.0f;
+        uint32_t vb, hb;
+        std::memcpy(&vb, &v, 4);
+        std::memcpy(&hb, &hh, 4);
+        a.wv[k] = ((uint64_t)vb << 32) | vb;
+        a.wh[k] = ((uint64_t)hb << 32) | hb;
+    }
+    const dim3 grid((unsigned)best.strips, (unsigned)bands, n_images);
+    int rc;
+    switch (C) {
+        case 1: rc = launch_c<1>(a, R, A, grid, best.threads, best.smem, st); break;
+        case 2: rc = launch_c<2>(a, R, A, grid, best.threads, best.smem, st); break;
+        case 3: rc = launch_c<3>(a, R, A, grid, best.threads, best.smem, st); break;
+        default: rc = launch_c<4>(a, R, A, grid, best.threads, best.smem, st); break;
+    }
+    return rc ? rc : 1;
+}
+
+}  // namespace b200

@@ -84,6 +84,11 @@ typedef enum {
 /* Resampler only: use the tile kernel even where the column-streaming kernel (downscales of
  * u8 / u16 images) applies.  Same results; exists so that both kernels can be tested. */
 #define B200IMG_RESIZE_TILED 512
+/* Resampler only: do not use the kernel for u8 downscales by an even integer ratio (2x, 4x; fixed
+ * window shape, one weight vector per axis, border windows renormalised after the sum) but the
+ * table-driven kernels that serve every other size.  Both are within the FAST contract (+-1 LSB
+ * of the reference); they may differ from each other by rounding.  For tests. */
+#define B200IMG_RESIZE_GENERAL 8192
 /* thumbnail only: evaluate every output pixel on its own (the kernel that serves upscales and
  * unaligned rows) even where the column-sum kernel applies.  Same results; for tests. */
 #define B200IMG_THUMBNAIL_PER_PIXEL 1024

@@ -195,3 +195,70 @@ def test_large_image_linearity_property(cuda):
     idx_v = torch.from_numpy(l_v.astype(np.int64)).to(cuda)
     idx_h = torch.from_numpy(l_h.astype(np.int64)).to(cuda)
     assert torch.equal(near, rnd[idx_v][:, idx_h])
+
+
+def _int_ratio_check(img, r, f, cuda, acc_init=1.0):
+    """u8 downscale by the even integer ratio r: the fixed-window kernel (default) and the table-driven kernels
+    (RESIZE_GENERAL) are both within +-1 LSB of the oracle."""
+    import torch
+    h, w = img.shape[:2]
+    nw, nh = w // r, h // r
+    want = o.resize(img, nw, nh, int(f), acc_init=acc_init).astype(np.int64)
+    src = torch.from_numpy(img).to(cuda)
+    fast = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_FAST).cpu().numpy().astype(np.int64)
+    general = imageops.resize(src, nw, nh, f, acc_init=acc_init, flags=L.FP_FAST | L.RESIZE_GENERAL).cpu().numpy().astype(np.int64)
+    d = np.abs(fast - want)
+    assert d.max() <= 1, f"{f.name} r={r} {img.shape}: max|d|={d.max()} at {np.argwhere(d > 1)[:5].tolist()}"
+    assert np.abs(general - want).max() <= 1
+    return float((d > 0).mean())
+
+
+@pytest.mark.parametrize("f", [FilterType.Triangle, FilterType.CatmullRom, FilterType.Gaussian, FilterType.Lanczos3])
+@pytest.mark.parametrize("c", [1, 2, 3, 4])
+@pytest.mark.parametrize("r", [2, 4])
+def test_resize_integer_ratio_u8(cuda, f, c, r):
+    """Even integer ratios run the fixed-window kernel (resample_int.cu): every filter, channel count, ragged strip and
+    band ends, images smaller than a window, and both accumulator start values (sample.rs:547)."""
+    rng = np.random.default_rng(100 * r + 10 * c + int(f))
+    off = 0.0
+    for (w, h) in [(1920, 1080), (r * 200 + 8 * r, r * 67), (r * 36, r * 500), (8 * r, 4 * r)]:
+        if (w * c) % 4:
+            w += 4 * r
+        img = rand_image(rng, h, w, c, np.uint8)
+        off = max(off, _int_ratio_check(img, r, f, cuda))
+    # extremes: a saturated image stays saturated (weights sum to one up to rounding), black stays black
+    for v in (0, 255):
+        img = np.full((r * 64, r * 320, c), v, np.uint8)
+        _int_ratio_check(img, r, f, cuda, acc_init=0.0)
+    assert off < 0.02  # +-1 LSB differences are rounding ties, not a bias
+
+
+def test_resize_integer_ratio_batch_and_bands(cuda):
+    """The batch entry point and the row-band entry point on the fixed-window kernel."""
+    import torch
+    rng = np.random.default_rng(77)
+    imgs = np.stack([rand_image(rng, 384, 512, 4, np.uint8) for _ in range(24)])
+    src = torch.from_numpy(imgs).to(cuda)
+    dst = torch.empty((24, 96, 128, 4), dtype=torch.uint8, device=cuda)
+    st = torch.cuda.current_stream().cuda_stream
+    lib = L.lib()
+    L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, 512, 384, 4, L.U8, dst.data_ptr(), 0, 128, 96, 24,
+                                         int(FilterType.CatmullRom), 1.0, L.FP_FAST, st))
+    got = dst.cpu().numpy()
+    for i in (0, 11, 23):
+        want = o.resize(imgs[i], 128, 96, int(FilterType.CatmullRom))
+        assert np.abs(got[i].astype(np.int64) - want.astype(np.int64)).max() <= 1
+    # bands of one large image: each band reads only the rows its outputs tap
+    img = rand_image(rng, 4000, 1024, 3, np.uint8)
+    want = o.resize(img, 512, 2000, int(FilterType.Lanczos3)).astype(np.int64)
+    out = np.zeros((2000, 512, 3), np.uint8)
+    import ctypes
+    for r0, rows in [(0, 700), (700, 601), (1301, 699)]:
+        s0, sn = ctypes.c_uint32(), ctypes.c_uint32()
+        L.check(lib.b200img_resize_band_src_rows(4000, 2000, int(FilterType.Lanczos3), r0, rows, ctypes.byref(s0), ctypes.byref(sn)))
+        band = torch.from_numpy(img[s0.value:s0.value + sn.value].copy()).to(cuda)
+        d = torch.empty((rows, 512, 3), dtype=torch.uint8, device=cuda)
+        L.check(lib.b200img_resize_band_dev(band.data_ptr(), s0.value, sn.value, 1024, 4000, 3, L.U8, d.data_ptr(), r0, rows,
+                                            512, 2000, int(FilterType.Lanczos3), 1.0, L.FP_FAST, st))
+        out[r0:r0 + rows] = d.cpu().numpy()
+    assert np.abs(out.astype(np.int64) - want).max() <= 1
