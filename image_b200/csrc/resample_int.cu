@@ -34,7 +34,9 @@ namespace b200 {
 namespace {
 
 constexpr int RI_THREADS = 320;  // word columns per strip, at most (the block is as wide as the strip needs)
+constexpr int RI_THREADS_PX = 256;  // ... of four-channel images (three CTAs per SM: 85 registers)
 constexpr int RI_MAX_TAPS = 24;
+constexpr int RI_MAX_BAND = 256;    // output rows per band, at most
 
 struct IntArgs {
     const void *src;
@@ -47,6 +49,7 @@ struct IntArgs {
     int tmp_pitch;      // floats per ring row (1 mod 32: lane = row reads hit 32 banks)
     int out_pitch;      // bytes per staged output row (4 * odd)
     float acc_init;
+    int vec_out;        // four-channel kernel: destination rows are 16-byte aligned (128-bit stores)
     f32x2 wv[RI_MAX_TAPS], wh[RI_MAX_TAPS];  // (w, w) pairs
 };
 
@@ -79,15 +82,19 @@ __device__ __forceinline__ uint32_t pack_u8x4(float r, float g, float b, float a
 }
 
 template <int C, int R, int A>
-__global__ void __launch_bounds__(RI_THREADS)
+__global__ void __launch_bounds__(C == 4 ? RI_THREADS_PX : RI_THREADS, C == 4 ? 3 : 1)
 resize_int_kernel(const __grid_constant__ IntArgs a) {
     constexpr int NT = A * R;            // taps
     constexpr int P = A * R;             // rows of one period of the vertical pass
-    constexpr int HR = A == 6 ? 30 : 32; // ring rows = output rows per horizontal phase (a multiple of A)
+    constexpr bool PX = C == 4;          // a source word is one pixel: the ring holds float4 pixels (128-bit stores and loads)
+    // ring rows = output rows per horizontal phase (a multiple of A).  The ring is what bounds the warps per SM (every thread
+    // column owns HR entries of it), and this kernel lives on issue slots: four-channel images keep 12 or 16 rows and let the
+    // two halves of a warp work on different pixel blocks (lane & 15 = row); the scalar layout needs all 32 lanes on one
+    // column for its bank pattern and keeps 30 or 32.
+    constexpr int HR = PX ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
     constexpr int PH = HR / A;           // periods per horizontal phase
     constexpr int D = P <= 16 ? P : P / 2;  // source rows in flight per thread (divides P: the row buffer is indexed statically)
     constexpr int SPAN = R * 7 + NT;     // samples the windows of 8 consecutive outputs span
-    constexpr bool PX = C == 4;          // a source word is one pixel: the ring holds float4 pixels (128-bit stores and loads)
     constexpr int PAD = PX ? 0 : 3;      // ring columns in front of the strip's first sample (the first word may start before it)
     static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
     extern __shared__ __align__(16) unsigned char smem[];
@@ -114,9 +121,6 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
     const int col0 = b0 + 4 * tid - p0 * C + PAD;  // ring column of this thread's first subpixel (>= 0: b0 was rounded down by < 4)
     const bool edge = p0 < 0 || p1 > (int)a.w;   // only strips that touch the image's left / right edge have clipped windows
 
-    // a ring of zeros: the columns of samples outside the image are never written and must contribute nothing
-    for (int i = tid; i < HR * a.tmp_pitch; i += nthreads) s_tmp[i] = 0.0f;
-    __syncthreads();
 
     // ---- vertical stream: row u of the stream is source row jbase + u, one virtual output in front of the band (so that
     // period m completes exactly the outputs (m - 1) A .. m A - 1); rows that no output of this band taps, and rows outside
@@ -145,7 +149,8 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
     float *const tflush0 = s_tmp + col0;
     float *tflush = tflush0;
     const int periods = (nout + A - 1) / A + 1;
-    const int rl = min(lane, HR - 1);  // lanes beyond the ring's last row recompute it (and store nothing)
+    const int rlane = PX ? (lane & 15) : lane;  // the ring row a lane works on in the horizontal pass
+    const int rl = min(rlane, HR - 1);           // lanes beyond the ring's last row recompute it (and store nothing)
 
     auto horizontal = [&](int n0, int rows_g) {
         // destination rows oyA + n0 .. + rows_g; their intermediates are ring rows 0 .. rows_g
@@ -155,7 +160,7 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
             // a warp item = one block of 8 pixels, all four channels: a 128-bit load per sample, (r, g) and (b, a) as packed pairs
             const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_tmp + (size_t)rl * a.tmp_pitch);
             uint32_t *orow = reinterpret_cast<uint32_t *>(s_out + (size_t)rl * a.out_pitch);
-            for (int item = warp; item < nb; item += nwarps) {
+            for (int item = 2 * warp + (lane >> 4); item < nb; item += 2 * nwarps) {
                 const int xa = item * 8;
                 const ulonglong2 *t = trow + R * xa;
                 f32x2 acc[8][2];
@@ -185,7 +190,7 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
                             r *= hs; g *= hs; b *= hs; al *= hs;
                         }
                     }
-                    if (lane < rows_g && xa + i < tw) orow[xa + i] = pack_u8x4(r, g, b, al);
+                    if (rlane < rows_g && xa + i < tw) orow[xa + i] = pack_u8x4(r, g, b, al);
                 }
             }
         } else {
@@ -241,6 +246,10 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
     uint32_t buf[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) buf[k] = load_next();
+    // a ring of zeros (while the first rows are on their way): the columns of samples outside the image are never written
+    // and must contribute nothing
+    for (int i = tid; i < HR * a.tmp_pitch; i += nthreads) s_tmp[i] = 0.0f;
+    __syncthreads();
     for (int m = 0; m < periods; ++m) {
 #pragma unroll
         for (int q = 0; q < P; ++q) {   // q is a compile-time constant after unrolling
@@ -296,6 +305,184 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
     }
 }
 
+// ---- four-channel images: a source word is one pixel ----
+// The same two passes with a float4 ring: the vertical pass stores a pixel with one 128-bit store, the horizontal pass
+// loads one with one 128-bit load as two packed pairs (r, g) (b, a), and writes its 8 output pixels (32 contiguous bytes per
+// row) straight to global memory.  The ring is double buffered: a warp goes from its share of the horizontal pass of one
+// phase straight into the vertical pass of the next, which fills the other buffer, so a phase costs one CTA barrier.
+// Nothing in the row loop branches: border scales come from a small table in shared memory, threads beyond the strip's
+// last word store to a dump slot, rows that no output needs are stored and never read.
+template <int R, int A>
+__global__ void __launch_bounds__(RI_THREADS_PX, 3)
+resize_int4_kernel(const __grid_constant__ IntArgs a) {
+    constexpr int NT = A * R, P = A * R;
+    constexpr int HR = A == 6 ? 12 : 16;   // ring rows per buffer = output rows per horizontal phase; lane & 15 = row
+    constexpr int PH = HR / A;
+    constexpr int D = P <= 16 ? P : P / 2;
+    constexpr int SPAN = R * 7 + NT;
+    static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
+    extern __shared__ __align__(16) unsigned char smem[];
+    float *s_ring = reinterpret_cast<float *>(smem);                 // [2][HR][tmp_pitch]
+    float *s_dump = s_ring + (size_t)2 * HR * a.tmp_pitch;           // 4 floats
+    float *s_vs = s_dump + 4;                                        // [BAND + 2 A]: vertical border scale of output n at [n + A]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
+    const unsigned img = blockIdx.z;
+    const int ox0 = blockIdx.x * a.TW;
+    const int tw = min(a.TW, (int)a.nw - ox0);
+    const int oyA = (int)a.dst_row0 + blockIdx.y * a.BAND;
+    const int nout = min(a.BAND, (int)(a.dst_row0 + a.dst_rows) - oyA);
+    if (nout <= 0) return;
+
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(a.src) + (size_t)img * a.src_img_stride;
+    uint8_t *dst = reinterpret_cast<uint8_t *>(a.dst) + (size_t)img * a.dst_img_stride;
+    const size_t gp = (size_t)a.w * 4;
+    const int p0 = R * ox0 + a.L0h;              // source pixel of ring column 0 (may be negative)
+    const int p1 = R * (ox0 + tw - 1) + a.L0h + NT;
+    const int q0 = max(p0, 0), q1 = min(p1, (int)a.w);
+    const bool active = tid < q1 - q0;           // <= blockDim.x pixels (the host's choice of TW)
+    const bool edge = p0 < 0 || p1 > (int)a.w;
+
+    const int jbase = R * oyA + a.L0v - R;
+    const int ulo = max(R * oyA + a.L0v, 0) - jbase;
+    const unsigned ulen = (unsigned)(min((int)a.h, R * (oyA + nout - 1) + a.L0v + NT) - jbase - ulo);
+    const uint8_t *gptr = src + 4 * (size_t)(q0 + (active ? tid : 0)) + ((ptrdiff_t)jbase - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
+    int unext = 0;
+    auto load_next = [&]() -> uint32_t {
+        uint32_t v = 0u;
+        if ((unsigned)(unext - ulo) < ulen) v = __ldg(reinterpret_cast<const uint32_t *>(gptr));
+        gptr += gp;
+        ++unext;
+        return v;
+    };
+    uint32_t buf[D];
+#pragma unroll
+    for (int k = 0; k < D; ++k) buf[k] = load_next();
+
+    // while the first rows are on their way: a ring of zeros (the columns of samples outside the image are never written and
+    // must contribute nothing) and the border scales of this band's rows
+    for (int i = tid; i < 2 * HR * a.tmp_pitch + 4; i += nthreads) s_ring[i] = 0.0f;
+    for (int i = tid; i < a.BAND + 2 * A; i += nthreads) {
+        const int n = i - A, first = R * (oyA + n) + a.L0v;
+        float vs = 1.0f;
+        if (n >= 0 && n < nout && (first < 0 || first + NT > (int)a.h)) vs = border_scale<NT>(a.wv, first, (int)a.h);
+        s_vs[i] = vs;
+    }
+    __syncthreads();
+
+    f32x2 lo[A], hi[A];
+#pragma unroll
+    for (int s = 0; s < A; ++s) { lo[s] = 0ull; hi[s] = 0ull; }
+    const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+    const f32x2 init2 = pack2(a.acc_init, a.acc_init);
+    const int pitch_eff = active ? a.tmp_pitch : 0;
+    float *const tb0 = active ? s_ring + 4 * (q0 - p0 + tid) : s_dump;
+    float *const tb1 = active ? tb0 + (size_t)HR * a.tmp_pitch : s_dump;
+    float *tflush = tb0;
+    int phase = 0;                       // horizontal phases done: the vertical pass fills buffer phase & 1
+    const int rlane = lane & 15, rl = min(rlane, HR - 1);
+    const bool vec_out = a.vec_out != 0;
+
+    auto horizontal = [&](int n0, int rows_g) {
+        // destination rows oyA + n0 .. + rows_g from the buffer just filled
+        __syncthreads();
+        const int nb = a.TW >> 3;
+        const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_ring + ((size_t)(phase & 1) * HR + rl) * a.tmp_pitch);
+        uint8_t *grow = dst + (size_t)(oyA + n0 + rl - (int)a.dst_row0) * ((size_t)a.nw * 4) + (size_t)ox0 * 4;
+        for (int item = 2 * warp + (lane >> 4); item < nb; item += 2 * nwarps) {
+            const int xa = item * 8;
+            const ulonglong2 *t = trow + R * xa;
+            f32x2 acc[8][2];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { acc[i][0] = 0ull; acc[i][1] = 0ull; }
+#pragma unroll
+            for (int e = 0; e < SPAN; ++e) {
+                const ulonglong2 px = t[e];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = e - R * i;
+                    if (k >= 0 && k < NT) {
+                        acc[i][0] = fma2(px.x, RI_SYM(a.wh, k), acc[i][0]);
+                        acc[i][1] = fma2(px.y, RI_SYM(a.wh, k), acc[i][1]);
+                    }
+                }
+            }
+            if (edge) {   // strips on the image's left / right edge: some windows were clipped
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int first = R * (ox0 + xa + i) + a.L0h;
+                    if (first < 0 || first + NT > (int)a.w) {
+                        const float hs = border_scale<NT>(a.wh, first, (int)a.w);
+                        const f32x2 hs2 = pack2(hs, hs);
+                        acc[i][0] = fma2(acc[i][0], hs2, 0ull);
+                        acc[i][1] = fma2(acc[i][1], hs2, 0ull);
+                    }
+                }
+            }
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float r, g, b, al;
+                unpack2(acc[i][0], r, g);
+                unpack2(acc[i][1], b, al);
+                o[i] = pack_u8x4(r, g, b, al);
+            }
+            if (rlane < rows_g) {
+                uint32_t *gout = reinterpret_cast<uint32_t *>(grow) + xa;
+                if (vec_out && xa + 8 <= tw) {
+                    reinterpret_cast<uint4 *>(gout)[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                    reinterpret_cast<uint4 *>(gout)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        if (xa + i < tw) gout[i] = o[i];
+                }
+            }
+        }
+        ++phase;
+        tflush = (phase & 1) ? tb1 : tb0;
+    };
+
+    const int periods = (nout + A - 1) / A + 1;
+    for (int m = 0; m < periods; ++m) {
+        const float *vsp = s_vs + m * A;
+#pragma unroll
+        for (int q = 0; q < P; ++q) {   // q is a compile-time constant after unrolling
+            float f[4];
+            Word<uint8_t>::biased(buf[q % D], f);
+            buf[q % D] = load_next();
+            const f32x2 f01 = add2(pack2(f[0], f[1]), bias2), f23 = add2(pack2(f[2], f[3]), bias2);
+            const int fq = q / R, qr = q % R;
+#pragma unroll
+            for (int aa = 0; aa < A; ++aa) {
+                const int slot = ((fq - aa) % A + A) % A, tap = qr + R * aa;
+                lo[slot] = fma2(f01, RI_SYM(a.wv, tap), lo[slot]);
+                hi[slot] = fma2(f23, RI_SYM(a.wv, tap), hi[slot]);
+            }
+            if (qr == R - 1) {   // output row n = (m - 1) A + fq is complete, in accumulator (fq + 1) mod A
+                const int fs = (fq + 1) % A;
+                const float vs = vsp[fq];
+                const f32x2 vs2 = pack2(vs, vs);
+                *reinterpret_cast<ulonglong2 *>(tflush) = make_ulonglong2(fma2(lo[fs], vs2, init2), fma2(hi[fs], vs2, init2));
+                tflush += pitch_eff;
+                lo[fs] = 0ull;
+                hi[fs] = 0ull;
+            }
+        }
+        if (m == 0) {
+            tflush = tb0;  // period 0 completed only the virtual outputs in front of the band
+        } else {
+            // periods 1 .. m have completed outputs 0 .. m A - 1: a horizontal phase every PH periods and at the band's end
+            const int done = min(m * A, nout);
+            if ((m % PH) == 0 || done == nout) {
+                const int n0 = (done - 1) / HR * HR;
+                horizontal(n0, done - n0);
+                if (done == nout) break;
+            }
+        }
+    }
+}
+
 #undef RI_SYM
 
 // The window rule of one axis: every output o of [o0, o1) must tap exactly the samples of [R o + L0, R o + L0 + NT) that lie
@@ -340,13 +527,21 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
     int op = round_up_i(TW * C, 4);
     if ((op / 4) % 2 == 0) op += 4;
     g.out_pitch = op;
-    g.smem = (size_t)HR * tp * 4 + (size_t)HR * op;
+    if (C == 4) g.smem = (size_t)2 * HR * tp * 4 + 16 + (size_t)(RI_MAX_BAND + 2 * 6) * 4;  // two ring buffers, dump slot, border scales
+    else g.smem = (size_t)HR * tp * 4 + (size_t)HR * op;
     return g;
 }
 
 template <int C, int R, int A>
 int launch_ra(const IntArgs &a, dim3 grid, int threads, size_t smem, cudaStream_t st) {
-    auto k = resize_int_kernel<C, R, A>;
+    if constexpr (C == 4) {
+        auto k4 = resize_int4_kernel<R, A>;
+        B200_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k4<<<grid, threads, smem, st>>>(a);
+        B200_CUDA(cudaGetLastError());
+        return B200IMG_OK;
+    }
+    auto k = resize_int_kernel<C == 4 ? 3 : C, R, A>;
     B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k<<<grid, threads, smem, st>>>(a);
     B200_CUDA(cudaGetLastError());
@@ -399,16 +594,17 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     if (!axis_is_uniform(vt, (int)h, R, NT, L0v, dst_row0, dst_row0 + dst_rows, wvm)) return 0;
     if (!axis_is_uniform(ht, (int)w, R, NT, L0h, 0, nw, whm)) return 0;
 
-    const int HR = A == 6 ? 30 : 32;
+    const int HR = C == 4 ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
+    const int max_threads = C == 4 ? RI_THREADS_PX : RI_THREADS;
     // strip width: the fewest thread columns over the image's width among the widths that leave room for two CTAs per SM
     IntGeo best;
     const int forced_tw = env_int("B200IMG_RI_TW", 0);
     for (int pass = 0; pass < 2 && best.TW == 0; ++pass) {
-        const size_t cap = pass == 0 ? (size_t)(233472 - 2048) / 2 : ctx->smem_optin;
+        const size_t cap = pass == 0 ? (C == 4 ? (size_t)(233472 - 3072) / 3 : (size_t)(233472 - 2048) / 2) : ctx->smem_optin;
         for (int TW = 16; TW <= 256; TW += 16) {
             if (forced_tw && TW != forced_tw) continue;
             const IntGeo g = int_geo(TW, w, nw, C, R, NT, L0h, HR);
-            if (g.threads > RI_THREADS || g.smem > std::min(cap, ctx->smem_optin)) continue;
+            if (g.threads > max_threads || g.smem > std::min(cap, ctx->smem_optin)) continue;
             if (best.TW == 0 || (int64_t)g.threads * g.strips < (int64_t)best.threads * best.strips ||
                 ((int64_t)g.threads * g.strips == (int64_t)best.threads * best.strips && TW > best.TW))
                 best = g;
@@ -416,9 +612,9 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     }
     if (best.TW == 0) return 0;
     const int ctas_per_sm = std::max<int>(1, std::min<size_t>(2048 / best.threads, (233472 - 1024) / (best.smem + 1024)));
-    int BAND = 4 * HR;
+    int BAND = 120 / HR * HR;
     const int forced_band = env_int("B200IMG_RI_BAND", 0);
-    if (forced_band > 0) BAND = round_up_i(forced_band, HR);
+    if (forced_band > 0) BAND = std::min(round_up_i(forced_band, HR), RI_MAX_BAND / HR * HR);
     else
         while (BAND > HR && (uint64_t)best.strips * ((dst_rows + BAND - 1) / BAND) * n_images < (uint64_t)ctx->sm_count * ctas_per_sm * 3) BAND -= HR;
     const int bands = (int)((dst_rows + BAND - 1) / BAND);
@@ -430,6 +626,7 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     a.w = w; a.h = h; a.nw = nw; a.nh = nh; a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
     a.L0v = L0v; a.L0h = L0h; a.TW = best.TW; a.BAND = BAND; a.tmp_pitch = best.tmp_pitch; a.out_pitch = best.out_pitch;
     a.acc_init = acc_init;
+    a.vec_out = ((size_t)nw * C) % 16 == 0 && dst_img_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
     for (int k = 0; k < RI_MAX_TAPS; ++k) {
         const float v = k < NT ? wvm[k] : 0.0f, hh = k < NT ? whm[k] : 0.0f;
         uint32_t vb, hb;

@@ -17,7 +17,7 @@ if name in ("k4", "k1", "k5"):
     if name == "k4":
         n, w, h, nw, nh, f, dt, tdt = 64, 1024, 1024, 256, 256, FilterType.CatmullRom, L.U8, torch.uint8
     elif name == "k1":
-        n, w, h, nw, nh, f, dt, tdt = 16, 1920, 1080, 960, 540, FilterType.Lanczos3, L.U8, torch.uint8
+        n, w, h, nw, nh, f, dt, tdt = 64, 1920, 1080, 960, 540, FilterType.Lanczos3, L.U8, torch.uint8
     else:
         n, w, h, nw, nh, f, dt, tdt = 1, 4096, 2048, 8192, 4096, FilterType.Lanczos3, L.F32, torch.float32
     src = (torch.rand((n, h, w, 4), device=dev, generator=g) * (255 if tdt == torch.uint8 else 1)).to(tdt)
