@@ -34,7 +34,7 @@ namespace b200 {
 namespace {
 
 constexpr int RI_THREADS = 320;  // word columns per strip, at most (the block is as wide as the strip needs)
-constexpr int RI_THREADS_PX = 256;  // ... of four-channel images (three CTAs per SM: 85 registers)
+constexpr int RI_THREADS_PX = 224;  // ... of four-channel images (three CTAs per SM: 96 registers)
 constexpr int RI_MAX_TAPS = 24;
 constexpr int RI_MAX_BAND = 256;    // output rows per band, at most
 
@@ -82,20 +82,16 @@ __device__ __forceinline__ uint32_t pack_u8x4(float r, float g, float b, float a
 }
 
 template <int C, int R, int A>
-__global__ void __launch_bounds__(C == 4 ? RI_THREADS_PX : RI_THREADS, C == 4 ? 3 : 1)
+__global__ void __launch_bounds__(RI_THREADS)
 resize_int_kernel(const __grid_constant__ IntArgs a) {
     constexpr int NT = A * R;            // taps
     constexpr int P = A * R;             // rows of one period of the vertical pass
-    constexpr bool PX = C == 4;          // a source word is one pixel: the ring holds float4 pixels (128-bit stores and loads)
-    // ring rows = output rows per horizontal phase (a multiple of A).  The ring is what bounds the warps per SM (every thread
-    // column owns HR entries of it), and this kernel lives on issue slots: four-channel images keep 12 or 16 rows and let the
-    // two halves of a warp work on different pixel blocks (lane & 15 = row); the scalar layout needs all 32 lanes on one
-    // column for its bank pattern and keeps 30 or 32.
-    constexpr int HR = PX ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
+    static_assert(C < 4, "four-channel images have their own kernel below");
+    constexpr int HR = A == 6 ? 30 : 32; // ring rows = output rows per horizontal phase (a multiple of A); lane = row
     constexpr int PH = HR / A;           // periods per horizontal phase
     constexpr int D = P <= 16 ? P : P / 2;  // source rows in flight per thread (divides P: the row buffer is indexed statically)
     constexpr int SPAN = R * 7 + NT;     // samples the windows of 8 consecutive outputs span
-    constexpr int PAD = PX ? 0 : 3;      // ring columns in front of the strip's first sample (the first word may start before it)
+    constexpr int PAD = 3;               // ring columns in front of the strip's first sample (the first word may start before it)
     static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
     extern __shared__ __align__(16) unsigned char smem[];
     float *s_tmp = reinterpret_cast<float *>(smem);                                    // [HR][tmp_pitch]
@@ -149,51 +145,13 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
     float *const tflush0 = s_tmp + col0;
     float *tflush = tflush0;
     const int periods = (nout + A - 1) / A + 1;
-    const int rlane = PX ? (lane & 15) : lane;  // the ring row a lane works on in the horizontal pass
-    const int rl = min(rlane, HR - 1);           // lanes beyond the ring's last row recompute it (and store nothing)
+    const int rl = min(lane, HR - 1);  // lanes beyond the ring's last row recompute it (and store nothing)
 
     auto horizontal = [&](int n0, int rows_g) {
         // destination rows oyA + n0 .. + rows_g; their intermediates are ring rows 0 .. rows_g
         __syncthreads();
         const int nb = a.TW >> 3;                 // 8-pixel blocks per strip (even)
-        if constexpr (PX) {
-            // a warp item = one block of 8 pixels, all four channels: a 128-bit load per sample, (r, g) and (b, a) as packed pairs
-            const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_tmp + (size_t)rl * a.tmp_pitch);
-            uint32_t *orow = reinterpret_cast<uint32_t *>(s_out + (size_t)rl * a.out_pitch);
-            for (int item = 2 * warp + (lane >> 4); item < nb; item += 2 * nwarps) {
-                const int xa = item * 8;
-                const ulonglong2 *t = trow + R * xa;
-                f32x2 acc[8][2];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) { acc[i][0] = 0ull; acc[i][1] = 0ull; }
-#pragma unroll
-                for (int e = 0; e < SPAN; ++e) {
-                    const ulonglong2 px = t[e];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int k = e - R * i;
-                        if (k >= 0 && k < NT) {
-                            acc[i][0] = fma2(px.x, RI_SYM(a.wh, k), acc[i][0]);
-                            acc[i][1] = fma2(px.y, RI_SYM(a.wh, k), acc[i][1]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    float r, g, b, al;
-                    unpack2(acc[i][0], r, g);
-                    unpack2(acc[i][1], b, al);
-                    if (edge) {
-                        const int first = R * (ox0 + xa + i) + a.L0h;
-                        if (first < 0 || first + NT > (int)a.w) {
-                            const float hs = border_scale<NT>(a.wh, first, (int)a.w);
-                            r *= hs; g *= hs; b *= hs; al *= hs;
-                        }
-                    }
-                    if (rlane < rows_g && xa + i < tw) orow[xa + i] = pack_u8x4(r, g, b, al);
-                }
-            }
-        } else {
+        {
             // a warp item = two blocks of 8 pixels, one channel: the two blocks' samples as packed pairs
             const int pairs = (nb >> 1) * C;
             const float *trow = s_tmp + (size_t)rl * a.tmp_pitch + PAD;
@@ -274,9 +232,7 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
                     const f32x2 vs2 = pack2(vs, vs);
                     const f32x2 x = fma2(lo[fs], vs2, init2), y = fma2(hi[fs], vs2, init2);
                     if (active) {
-                        if constexpr (PX) {
-                            *reinterpret_cast<ulonglong2 *>(tflush) = make_ulonglong2(x, y);
-                        } else {
+                        {
                             float v0, v1, v2, v3;
                             unpack2(x, v0, v1);
                             unpack2(y, v2, v3);
@@ -313,13 +269,14 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
 // Nothing in the row loop branches: border scales come from a small table in shared memory, threads beyond the strip's
 // last word store to a dump slot, rows that no output needs are stored and never read.
 template <int R, int A>
-__global__ void __launch_bounds__(RI_THREADS_PX, 3)
+__global__ void __maxnreg__(96)  // three CTAs of RI_THREADS_PX threads per SM
 resize_int4_kernel(const __grid_constant__ IntArgs a) {
     constexpr int NT = A * R, P = A * R;
     constexpr int HR = A == 6 ? 12 : 16;   // ring rows per buffer = output rows per horizontal phase; lane & 15 = row
     constexpr int PH = HR / A;
     constexpr int D = P <= 16 ? P : P / 2;
-    constexpr int SPAN = R * 7 + NT;
+    constexpr int BLK = R == 2 ? 8 : 4;     // output pixels per horizontal item: about two items per warp of thread columns
+    constexpr int SPAN = R * (BLK - 1) + NT;
     static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
     extern __shared__ __align__(16) unsigned char smem[];
     float *s_ring = reinterpret_cast<float *>(smem);                 // [2][HR][tmp_pitch]
@@ -386,20 +343,20 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
     auto horizontal = [&](int n0, int rows_g) {
         // destination rows oyA + n0 .. + rows_g from the buffer just filled
         __syncthreads();
-        const int nb = a.TW >> 3;
+        const int nb = (a.TW + BLK - 1) / BLK;
         const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_ring + ((size_t)(phase & 1) * HR + rl) * a.tmp_pitch);
         uint8_t *grow = dst + (size_t)(oyA + n0 + rl - (int)a.dst_row0) * ((size_t)a.nw * 4) + (size_t)ox0 * 4;
         for (int item = 2 * warp + (lane >> 4); item < nb; item += 2 * nwarps) {
-            const int xa = item * 8;
+            const int xa = item * BLK;
             const ulonglong2 *t = trow + R * xa;
-            f32x2 acc[8][2];
+            f32x2 acc[BLK][2];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { acc[i][0] = 0ull; acc[i][1] = 0ull; }
+            for (int i = 0; i < BLK; ++i) { acc[i][0] = 0ull; acc[i][1] = 0ull; }
 #pragma unroll
             for (int e = 0; e < SPAN; ++e) {
                 const ulonglong2 px = t[e];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
+                for (int i = 0; i < BLK; ++i) {
                     const int k = e - R * i;
                     if (k >= 0 && k < NT) {
                         acc[i][0] = fma2(px.x, RI_SYM(a.wh, k), acc[i][0]);
@@ -409,7 +366,7 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
             }
             if (edge) {   // strips on the image's left / right edge: some windows were clipped
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
+                for (int i = 0; i < BLK; ++i) {
                     const int first = R * (ox0 + xa + i) + a.L0h;
                     if (first < 0 || first + NT > (int)a.w) {
                         const float hs = border_scale<NT>(a.wh, first, (int)a.w);
@@ -419,9 +376,9 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
                     }
                 }
             }
-            uint32_t o[8];
+            uint32_t o[BLK];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < BLK; ++i) {
                 float r, g, b, al;
                 unpack2(acc[i][0], r, g);
                 unpack2(acc[i][1], b, al);
@@ -429,12 +386,12 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
             }
             if (rlane < rows_g) {
                 uint32_t *gout = reinterpret_cast<uint32_t *>(grow) + xa;
-                if (vec_out && xa + 8 <= tw) {
-                    reinterpret_cast<uint4 *>(gout)[0] = make_uint4(o[0], o[1], o[2], o[3]);
-                    reinterpret_cast<uint4 *>(gout)[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                if (vec_out && xa + BLK <= tw) {
+#pragma unroll
+                    for (int i = 0; i < BLK; i += 4) reinterpret_cast<uint4 *>(gout + i)[0] = make_uint4(o[i], o[i + 1], o[i + 2], o[i + 3]);
                 } else {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
+                    for (int i = 0; i < BLK; ++i)
                         if (xa + i < tw) gout[i] = o[i];
                 }
             }
@@ -501,6 +458,7 @@ int round_up_i(int v, int m) { return (v + m - 1) / m * m; }
 struct IntGeo {
     int TW = 0, threads = 0, strips = 0, tmp_pitch = 0, out_pitch = 0;
     size_t smem = 0;
+    double cost = 0.0;  // issue slots per output row of the image, up to a constant
 };
 
 IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, int HR) {
@@ -517,7 +475,8 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
     g.threads = round_up_i(words, 32);
     int tp;
     if (C == 4) {  // float4 pixels: an odd number of pixels per row, so that the 128-bit loads of 8 rows hit 8 bank groups
-        const int px = R * (TW - 1) + NT;
+        const int blk = R == 2 ? 8 : 4;
+        const int px = R * (round_up_i(TW, blk) - 1) + NT;  // the last item reads its whole span
         tp = 4 * (px | 1);
     } else {
         tp = 3 + (R * (TW - 1) + NT) * C + 3;
@@ -529,6 +488,15 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
     g.out_pitch = op;
     if (C == 4) g.smem = (size_t)2 * HR * tp * 4 + 16 + (size_t)(RI_MAX_BAND + 2 * 6) * 4;  // two ring buffers, dump slot, border scales
     else g.smem = (size_t)HR * tp * 4 + (size_t)HR * op;
+    // every warp of the CTA walks HR * R source rows per phase, then the CTA's horizontal items go round its warps
+    const int nwarps = g.threads / 32;
+    if (C == 4) {
+        const int blk = R == 2 ? 8 : 4, nb = (TW + blk - 1) / blk, rounds = (nb + 2 * nwarps - 1) / (2 * nwarps);
+        const int A = NT / R, item = (R * (blk - 1) + NT) + 2 * blk * NT + 22 * blk + 40;
+        g.cost = (double)g.strips * nwarps * (HR * R * (10 + 2 * A + 12.0 / R) + rounds * item) / HR;
+    } else {
+        g.cost = (double)g.threads * g.strips;
+    }
     return g;
 }
 
@@ -596,27 +564,33 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
 
     const int HR = C == 4 ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
     const int max_threads = C == 4 ? RI_THREADS_PX : RI_THREADS;
-    // strip width: the fewest thread columns over the image's width among the widths that leave room for two CTAs per SM
+    // strip width: the cheapest (fewest thread columns over the image's width; for four channels also whole rounds of
+    // horizontal items) among the widths that leave room for two (three) CTAs per SM
     IntGeo best;
     const int forced_tw = env_int("B200IMG_RI_TW", 0);
     for (int pass = 0; pass < 2 && best.TW == 0; ++pass) {
         const size_t cap = pass == 0 ? (C == 4 ? (size_t)(233472 - 3072) / 3 : (size_t)(233472 - 2048) / 2) : ctx->smem_optin;
-        for (int TW = 16; TW <= 256; TW += 16) {
+        const int step = C == 4 ? (R == 2 ? 8 : 4) : 16;  // whole horizontal items (and 16-byte aligned output blocks)
+        for (int TW = step; TW <= 256; TW += step) {
             if (forced_tw && TW != forced_tw) continue;
             const IntGeo g = int_geo(TW, w, nw, C, R, NT, L0h, HR);
             if (g.threads > max_threads || g.smem > std::min(cap, ctx->smem_optin)) continue;
-            if (best.TW == 0 || (int64_t)g.threads * g.strips < (int64_t)best.threads * best.strips ||
-                ((int64_t)g.threads * g.strips == (int64_t)best.threads * best.strips && TW > best.TW))
-                best = g;
+            if (best.TW == 0 || g.cost < best.cost || (g.cost == best.cost && TW > best.TW)) best = g;
         }
     }
     if (best.TW == 0) return 0;
     const int ctas_per_sm = std::max<int>(1, std::min<size_t>(2048 / best.threads, (233472 - 1024) / (best.smem + 1024)));
-    int BAND = 120 / HR * HR;
+    // bands of about 128 output rows (the window overlap between bands costs (NT - R) source rows each), of equal height, and
+    // shorter ones when that leaves SMs without work
+    int BAND;
     const int forced_band = env_int("B200IMG_RI_BAND", 0);
-    if (forced_band > 0) BAND = std::min(round_up_i(forced_band, HR), RI_MAX_BAND / HR * HR);
-    else
+    if (forced_band > 0) {
+        BAND = std::min(round_up_i(forced_band, HR), RI_MAX_BAND / HR * HR);
+    } else {
+        int nbands = (int)((dst_rows + 127) / 128);
+        BAND = round_up_i((int)((dst_rows + nbands - 1) / nbands), HR);
         while (BAND > HR && (uint64_t)best.strips * ((dst_rows + BAND - 1) / BAND) * n_images < (uint64_t)ctx->sm_count * ctas_per_sm * 3) BAND -= HR;
+    }
     const int bands = (int)((dst_rows + BAND - 1) / BAND);
     if (bands > 65535 || n_images > 65535) return 0;
     if ((uint64_t)best.strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;  // a small single image: the tile kernels spread it better

@@ -25,8 +25,8 @@ def t(fn, n=20):
     return e0.elapsed_time(e1) / n
 
 
-CASES = [("K1", 64, 1920, 1080, 4, 960, 540, FilterType.Lanczos3, [48, 64, 80, 96, 112, 128], [30, 60, 90, 120, 180, 270]),
-         ("K4", 256, 1024, 1024, 4, 256, 256, FilterType.CatmullRom, [16, 32, 48, 64], [32, 64, 128, 256]),
+CASES = [("K1", 64, 1920, 1080, 4, 960, 540, FilterType.Lanczos3, [56, 64, 72, 80, 88, 96, 104], [60, 96, 120, 180]),
+         ("K4", 256, 1024, 1024, 4, 256, 256, FilterType.CatmullRom, [20, 28, 32, 36, 44, 52], [64, 112, 128, 256]),
          ("rgb8", 64, 1920, 1080, 3, 960, 540, FilterType.Lanczos3, [64, 80, 96, 112, 128, 160], [60, 120])]
 for name, n, w, h, c, nw, nh, f, tws, bands in CASES:
     src = torch.randint(0, 256, (n, h, w, c), dtype=torch.int32, device="cuda").to(torch.uint8)
