@@ -36,6 +36,11 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
                    size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
                    const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st);
 
+// resample_up2.cu: exact 2x upscales of four-channel f32 images with a support-3 filter (FAST arithmetic only)
+int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                   size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
+                   const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st);
+
 // resample_group.cu: tile kernel with four-sample groups on both axes (upscales, f32 images)
 void resize_group_release(int device);
 int resize_group_try(int filter, uint32_t h, const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, int C, int dtype, void *dst,
@@ -600,6 +605,9 @@ int resize_launch(const void *src, size_t src_stride, uint32_t src_row0, uint32_
     if (!(flags & (B200IMG_RESIZE_UNFUSED | B200IMG_RESIZE_TILED))) {
         if (!strict && !(flags & B200IMG_RESIZE_GENERAL)) {
             rc = resize_int_try(src, a.src_img_stride, src_row0, w, h, C, dtype, dst, a.dst_img_stride, dst_row0, dst_rows, nw, nh,
+                                n_images, vt->host, ht->host, acc_init, ctx, st);
+            if (rc != 0) return rc < 0 ? rc : B200IMG_OK;
+            rc = resize_up2_try(src, a.src_img_stride, src_row0, w, h, C, dtype, dst, a.dst_img_stride, dst_row0, dst_rows, nw, nh,
                                 n_images, vt->host, ht->host, acc_init, ctx, st);
             if (rc != 0) return rc < 0 ? rc : B200IMG_OK;
         }

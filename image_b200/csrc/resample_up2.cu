@@ -1,0 +1,310 @@
+// resample_up2.cu -- the resampler for exact 2x upscales of four-channel f32 images with a support-3 filter
+// (Lanczos3, Gaussian) under B200IMG_FP_FAST: BASELINE config 4, the 32768^2 Rgba32F Lanczos3 upscale and its
+// row bands.
+//
+// At ratio 1/2 destination samples 2m and 2m+1 both tap the SAME seven source samples m-3 .. m+3
+// (vertical_sample / horizontal_sample, src/imageops/sample.rs:494-562, 217-340: centre m + 0.25 resp.
+// m + 0.75, support 3, so left = m - 3 and right = m + 4 for both), each with its own weight vector
+// (one of whose ends is a zero of the filter -- kept, as the reference keeps it).  So:
+//   vertical:   a thread owns one source pixel column (a float4) and streams down the source rows with a
+//               window of seven rows in registers.  The row loop is unrolled over 14 rows, so the window is a
+//               circular register file indexed at compile time (no moves); each step is one 128-bit load
+//               issued seven rows ahead, 28 FFMA2 with weights in uniform registers, and two 128-bit stores
+//               of the destination-row pair into a ring in shared memory.
+//   horizontal: every seven steps (14 ring rows) the warps share out (row, 32 source positions) items:
+//               lane = source position, seven 128-bit loads of neighbouring ring pixels, 28 FFMA2 for the two
+//               destination pixels 2x and 2x+1, stored as 32 contiguous bytes per lane (1 KB per warp).
+// The ring is double buffered, so a phase costs one CTA barrier.  The job is bound by its stores (64 bytes
+// written per 16 read); the arithmetic is ~160 thread instructions per source pixel.
+// Borders: samples outside the image count as zero and the sum is multiplied by 1 / (weights inside), the
+// reference's renormalisation of the clipped window up to f32 rounding (FAST contract: 1e-5 relative).  The
+// accumulator's start value acc_init (sample.rs:547) is added once after the vertical pass.
+#include "common.cuh"
+#include "host_tables.h"
+#include "packed.cuh"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+namespace {
+
+constexpr int U2_T = 7;          // taps
+constexpr int U2_S = 3;          // support
+constexpr int U2_THREADS = 128;  // source pixel columns of a strip, halo included
+constexpr int U2_HR = 2 * U2_T;  // ring rows per buffer = destination rows per phase (seven source steps)
+
+struct Up2Args {
+    const void *src;
+    void *dst;
+    size_t src_img_stride, dst_img_stride;  // bytes
+    uint32_t w, h, nw, nh;
+    uint32_t src_row0, dst_row0, dst_rows;
+    int TWS;            // source pixels per strip (<= U2_THREADS - 6)
+    int BANDS;          // source rows (= destination row pairs) per band, a multiple of 7
+    int pitch;          // ring pixels per row (odd)
+    float acc_init;
+    f32x2 wv[2][U2_T], wh[2][U2_T];  // (w, w) pairs; [phase][tap]
+};
+
+__device__ __forceinline__ float up2_lo(f32x2 v) { float a, b; unpack2(v, a, b); return a; }
+
+// 1 / (sum of the taps of the window [first, first + 7) that fall inside [0, len)); only for clipped windows
+__device__ __noinline__ float up2_border_scale(const f32x2 *w, int first, int len) {
+    const int k0 = max(0, -first), k1 = min(U2_T, len - first);
+    float s = 0.0f;
+#pragma unroll 1
+    for (int k = k0; k < k1; ++k) s += up2_lo(w[k]);
+    return 1.0f / s;
+}
+
+__global__ void __launch_bounds__(U2_THREADS, 3)
+resize_up2_kernel(const __grid_constant__ Up2Args a) {
+    constexpr int T = U2_T, S = U2_S, HR = U2_HR;
+    extern __shared__ __align__(16) unsigned char smem[];
+    ulonglong2 *s_ring = reinterpret_cast<ulonglong2 *>(smem);            // [2][HR][pitch] float4 pixels
+    ulonglong2 *s_dump = s_ring + (size_t)2 * HR * a.pitch;               // one pixel
+    float *s_vs = reinterpret_cast<float *>(s_dump + 1);                  // [2 BANDS + 2 HR]: border scale of local destination row n at [n + HR]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nwarps = U2_THREADS / 32;
+    const unsigned img = blockIdx.z;
+    const int x0 = blockIdx.x * a.TWS;                 // first source pixel of the strip
+    const int tws = min(a.TWS, (int)a.w - x0);
+    const int m_lo = (int)a.dst_row0 >> 1;             // source row of the first destination pair this call touches
+    const int mA = m_lo + blockIdx.y * a.BANDS;
+    const int m_end = (int)((a.dst_row0 + a.dst_rows + 1) >> 1);
+    const int nm = min(a.BANDS, m_end - mA);           // destination pairs of this band
+    if (nm <= 0) return;
+
+    const float *src = reinterpret_cast<const float *>(reinterpret_cast<const unsigned char *>(a.src) + (size_t)img * a.src_img_stride);
+    float *dst = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(a.dst) + (size_t)img * a.dst_img_stride);
+    const int p0 = x0 - S;                             // source pixel of ring column 0
+    const int px = p0 + tid;                           // this thread's source pixel
+    const bool active = tid < tws + 2 * S && px >= 0 && px < (int)a.w;
+    const bool edge = p0 < 0 || x0 + tws + S > (int)a.w;
+
+    // ---- vertical stream: step u consumes source row j0 + u and completes the pair m = j0 + u - 3; the first seven steps
+    // only fill the window (their pairs lie in front of the band and are never read) ----
+    const int j0 = mA + S - T;
+    const int steps = T * (1 + (nm + T - 1) / T);
+    const size_t gp = (size_t)a.w * 4;                 // floats per source row
+    const float *gptr = src + (size_t)4 * (active ? px : max(min(px, (int)a.w - 1), 0)) + ((ptrdiff_t)j0 - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
+    int jnext = j0;
+    auto load_next = [&]() -> ulonglong2 {
+        ulonglong2 v = make_ulonglong2(0ull, 0ull);
+        if (jnext >= 0 && jnext < (int)a.h && jnext < mA + nm + S) v = __ldg(reinterpret_cast<const ulonglong2 *>(gptr));
+        gptr += gp;
+        ++jnext;
+        return v;
+    };
+    ulonglong2 R[2 * T];   // circular window: row j0 + u lives in R[u % 14]
+#pragma unroll
+    for (int k = 0; k < 2 * T; ++k) R[k] = make_ulonglong2(0ull, 0ull);
+#pragma unroll
+    for (int k = 0; k < T; ++k) R[k] = load_next();
+
+    for (int i = tid; i < (2 * HR * a.pitch + 1) * 4; i += U2_THREADS) reinterpret_cast<float *>(s_ring)[i] = 0.0f;
+    for (int i = tid; i < 2 * a.BANDS + 2 * HR; i += U2_THREADS) {
+        const int n = i - HR, o = 2 * mA + n;          // local / global destination row
+        const int first = (o >> 1) - S;                // its window (o >= 0 wherever it matters)
+        float vs = 1.0f;
+        if (n >= 0 && n < 2 * nm && (first < 0 || first + T > (int)a.h)) vs = up2_border_scale(a.wv[o & 1], first, (int)a.h);
+        s_vs[i] = vs;
+    }
+    __syncthreads();
+
+    const f32x2 init2 = pack2(a.acc_init, a.acc_init);
+    const int pitch_eff = active ? a.pitch : 0;
+    ulonglong2 *const tb0 = active ? s_ring + tid : s_dump;
+    ulonglong2 *const tb1 = active ? tb0 + (size_t)HR * a.pitch : s_dump;
+    ulonglong2 *tflush = tb0;
+    int phase = 0;     // horizontal phases done
+    
+    auto horizontal = [&](int n0) {
+        // local destination rows n0 .. n0 + 14 from the buffer just filled.  A warp item = one ring row x 32 source positions:
+        // lane = source position, seven 128-bit loads (neighbouring lanes, no bank conflicts), both phases' pixels from them,
+        // stored as 32 contiguous bytes per lane: a warp writes 1 KB of one destination row.
+        __syncthreads();
+        const int segs = (tws + 31) >> 5;
+        const ulonglong2 *rbase = s_ring + (size_t)(phase & 1) * HR * a.pitch;
+        const int row_lo = (int)a.dst_row0 - (2 * mA + n0), row_hi = (int)(a.dst_row0 + a.dst_rows) - (2 * mA + n0);  // ring rows to store
+        int rp = 0, seg = warp;              // item = (pair of ring rows, segment of 32 source positions)
+        while (seg >= segs) { seg -= segs; ++rp; }
+        while (rp < T) {
+            const int x = 32 * seg + lane;   // strip-local source position; ring column of x - 3
+            const ulonglong2 *t = rbase + (size_t)(2 * rp) * a.pitch + min(x, tws - 1);
+            f32x2 acc[2][2][2];              // [ring row of the pair][phase][half]
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr)
+#pragma unroll
+                for (int ph = 0; ph < 2; ++ph) { acc[rr][ph][0] = 0ull; acc[rr][ph][1] = 0ull; }
+#pragma unroll
+            for (int k = 0; k < T; ++k) {
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) {
+                    const ulonglong2 px4 = t[rr * a.pitch + k];
+#pragma unroll
+                    for (int ph = 0; ph < 2; ++ph) {
+                        acc[rr][ph][0] = fma2(px4.x, a.wh[ph][k], acc[rr][ph][0]);
+                        acc[rr][ph][1] = fma2(px4.y, a.wh[ph][k], acc[rr][ph][1]);
+                    }
+                }
+            }
+            if (edge) {   // strips on the image's left / right edge: some windows were clipped
+                const int first = x0 + x - S;
+                if (first < 0 || first + T > (int)a.w) {
+#pragma unroll
+                    for (int ph = 0; ph < 2; ++ph) {
+                        const float hs = up2_border_scale(a.wh[ph], first, (int)a.w);
+                        const f32x2 hs2 = pack2(hs, hs);
+#pragma unroll
+                        for (int rr = 0; rr < 2; ++rr) {
+                            acc[rr][ph][0] = fma2(acc[rr][ph][0], hs2, 0ull);
+                            acc[rr][ph][1] = fma2(acc[rr][ph][1], hs2, 0ull);
+                        }
+                    }
+                }
+            }
+            if (x < tws) {
+                float4 *gout = reinterpret_cast<float4 *>(dst + ((size_t)(2 * rp - row_lo) * a.nw + 2 * (size_t)(x0 + x)) * 4);
+#pragma unroll
+                for (int rr = 0; rr < 2; ++rr) {
+                    if (2 * rp + rr >= row_lo && 2 * rp + rr < row_hi) {
+#pragma unroll
+                        for (int ph = 0; ph < 2; ++ph) {
+                            float r, g, b, al;
+                            unpack2(acc[rr][ph][0], r, g);
+                            unpack2(acc[rr][ph][1], b, al);
+                            gout[(size_t)rr * (a.nw) + ph] = make_float4(Px<float>::clamp_nearest(r), Px<float>::clamp_nearest(g),
+                                                                         Px<float>::clamp_nearest(b), Px<float>::clamp_nearest(al));
+                        }
+                    }
+                }
+            }
+            seg += nwarps;
+            while (seg >= segs) { seg -= segs; ++rp; }
+        }
+        ++phase;
+        tflush = (phase & 1) ? tb1 : tb0;
+    };
+
+    for (int u0 = 0; u0 < steps; u0 += 2 * T) {
+        const float *vsp = s_vs + 2 * u0;   // pair of step u: local rows 2 (u - 7), + 1 -> s_vs[2 u], [2 u + 1]
+#pragma unroll
+        for (int s = 0; s < 2 * T; ++s) {   // s is a compile-time constant after unrolling
+            // the row loaded seven steps ago is in R[s]; fetch the one seven steps ahead into the slot that has just left the window
+            R[(s + T) % (2 * T)] = load_next();
+            f32x2 o[2][2];
+#pragma unroll
+            for (int ph = 0; ph < 2; ++ph) { o[ph][0] = 0ull; o[ph][1] = 0ull; }
+#pragma unroll
+            for (int k = 0; k < T; ++k) {
+                const ulonglong2 v = R[(s - (T - 1) + k + 2 * T) % (2 * T)];
+#pragma unroll
+                for (int ph = 0; ph < 2; ++ph) {
+                    o[ph][0] = fma2(v.x, a.wv[ph][k], o[ph][0]);
+                    o[ph][1] = fma2(v.y, a.wv[ph][k], o[ph][1]);
+                }
+            }
+#pragma unroll
+            for (int ph = 0; ph < 2; ++ph) {
+                const float vs = vsp[2 * s + ph];
+                const f32x2 vs2 = pack2(vs, vs);
+                *tflush = make_ulonglong2(fma2(o[ph][0], vs2, init2), fma2(o[ph][1], vs2, init2));
+                tflush += pitch_eff;
+            }
+            if (s == T - 1 || s == 2 * T - 1) {   // a phase of seven steps is complete
+                const int u = u0 + s;
+                if (u < T) {
+                    tflush = tb0;                 // the window-filling phase
+                } else if (u < steps) {
+                    horizontal(2 * (u - (T - 1) - T));
+                }
+            }
+        }
+    }
+}
+
+// one axis of the reference's tables: destination o = 2 m + ph taps [m - 3, m + 4) clipped to the image, whole windows with
+// bitwise the weights of that phase's middle window
+bool up2_axis_ok(const AxisTable &t, int len, const float *w0, const float *w1) {
+    const int n = (int)t.left.size();
+    for (int o = 0; o < n; ++o) {
+        const int first = (o >> 1) - U2_S, l = std::max(first, 0), r = std::min(first + U2_T, len);
+        if (t.left[o] != l || t.count[o] != r - l) return false;
+        if (r - l == U2_T && std::memcmp(&t.w[(size_t)o * t.stride], (o & 1) ? w1 : w0, sizeof(float) * U2_T) != 0) return false;
+    }
+    return true;
+}
+
+int up2_env_int(const char *name, int dflt) {
+    const char *e = std::getenv(name);
+    return e && *e ? std::atoi(e) : dflt;
+}
+
+}  // namespace
+
+// Returns 1 if this kernel took the job (and launched it), 0 if it does not apply, < 0 on error.
+int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, uint32_t h, int C, int dtype, void *dst,
+                   size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
+                   const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st) {
+    if (dtype != B200IMG_F32 || C != 4) return 0;
+    if (nw != 2 * w || nh != 2 * h || w < 16 || h < 16) return 0;
+    if (vt.max_count != U2_T || ht.max_count != U2_T) return 0;
+    if ((reinterpret_cast<uintptr_t>(src) & 15) != 0 || (reinterpret_cast<uintptr_t>(dst) & 15) != 0 || src_img_stride % 16 != 0 ||
+        dst_img_stride % 16 != 0)
+        return 0;
+    if (w > (1u << 28) || h > (1u << 28)) return 0;  // int arithmetic in the kernel
+    // whole windows in the middle of each axis give the two weight vectors
+    const uint32_t vm = (nh / 2) & ~1u, hm = (nw / 2) & ~1u;
+    if (vt.count[vm] != U2_T || vt.count[vm + 1] != U2_T || ht.count[hm] != U2_T || ht.count[hm + 1] != U2_T) return 0;
+    const float *wv0 = &vt.w[(size_t)vm * vt.stride], *wv1 = &vt.w[(size_t)(vm + 1) * vt.stride];
+    const float *wh0 = &ht.w[(size_t)hm * ht.stride], *wh1 = &ht.w[(size_t)(hm + 1) * ht.stride];
+    if (!up2_axis_ok(vt, (int)h, wv0, wv1) || !up2_axis_ok(ht, (int)w, wh0, wh1)) return 0;
+
+    Up2Args a;
+    a.src = src; a.dst = dst; a.src_img_stride = src_img_stride; a.dst_img_stride = dst_img_stride;
+    a.w = w; a.h = h; a.nw = nw; a.nh = nh; a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
+    a.acc_init = acc_init;
+    // strip width: the widest that the block covers with its halo, narrowed so that the strips are of equal width (multiples of 4)
+    int TWS = U2_THREADS - 2 * U2_S;
+    const int strips0 = (int)((w + TWS - 1) / TWS);
+    TWS = std::min(TWS, (int)(((w + strips0 - 1) / strips0 + 3) & ~3u));
+    TWS = std::min(TWS, up2_env_int("B200IMG_U2_TWS", TWS)) & ~3;
+    if (TWS < 4) return 0;
+    a.TWS = TWS;
+    a.pitch = (4 * ((TWS + 3) / 4) + 2 * U2_S) | 1;
+    const int strips = (int)((w + TWS - 1) / TWS);
+    const int pairs = (int)(((dst_row0 + dst_rows + 1) >> 1) - (dst_row0 >> 1));
+    // rows per band: the job is bound by its stores and a CTA is a chain of short phases, so what matters is that the grid is
+    // many times the resident CTAs (B200: 4096^2 -> 8192^2 0.34 ms with 21-row bands, 0.41 with 84; 8192^2 best at 63)
+    int BANDS = 126;
+    while (BANDS > 3 * U2_T && (uint64_t)strips * ((pairs + BANDS - 1) / BANDS) * n_images < (uint64_t)ctx->sm_count * 48) BANDS -= U2_T;
+    {
+        const int forced = up2_env_int("B200IMG_U2_BANDS", 0);
+        if (forced > 0) BANDS = std::min((forced + U2_T - 1) / U2_T * U2_T, 252);
+    }
+    a.BANDS = BANDS;
+    const int bands = (pairs + BANDS - 1) / BANDS;
+    if (bands > 65535 || n_images > 65535) return 0;
+    if ((uint64_t)strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;  // a small image: the tile kernels spread it better
+    for (int ph = 0; ph < 2; ++ph)
+        for (int k = 0; k < U2_T; ++k) {
+            const float v = (ph ? wv1 : wv0)[k], hh = (ph ? wh1 : wh0)[k];
+            uint32_t vb, hb;
+            std::memcpy(&vb, &v, 4);
+            std::memcpy(&hb, &hh, 4);
+            a.wv[ph][k] = ((uint64_t)vb << 32) | vb;
+            a.wh[ph][k] = ((uint64_t)hb << 32) | hb;
+        }
+    const size_t smem = ((size_t)2 * U2_HR * a.pitch + 1) * 16 + (size_t)(2 * BANDS + 2 * U2_HR) * 4;
+    if (smem > ctx->smem_optin) return 0;
+    B200_CUDA(cudaFuncSetAttribute(resize_up2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    resize_up2_kernel<<<dim3((unsigned)strips, (unsigned)bands, n_images), U2_THREADS, smem, st>>>(a);
+    B200_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace b200

@@ -262,3 +262,44 @@ def test_resize_integer_ratio_batch_and_bands(cuda):
                                             512, 2000, int(FilterType.Lanczos3), 1.0, L.FP_FAST, st))
         out[r0:r0 + rows] = d.cpu().numpy()
     assert np.abs(out.astype(np.int64) - want).max() <= 1
+
+
+@pytest.mark.parametrize("f", [FilterType.Lanczos3, FilterType.Gaussian])
+def test_resize_up2_rgba32f(cuda, f):
+    """Exact 2x upscales of Rgba32F with a support-3 filter run the register-window kernel (resample_up2.cu): ragged strips
+    and bands, both accumulator start values, a batch, and row bands that start and end on odd destination rows."""
+    import ctypes
+    import torch
+    rng = np.random.default_rng(int(f))
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    for (h, w) in [(300, 517), (1031, 250), (64, 2048)]:
+        img = rand_image(rng, h, w, 4, np.float32)
+        for acc in (1.0, 0.0):
+            want = o.resize(img, 2 * w, 2 * h, int(f), acc_init=acc)
+            src = torch.from_numpy(img).to(cuda)
+            got = imageops.resize(src, 2 * w, 2 * h, f, acc_init=acc, flags=L.FP_FAST).cpu().numpy()
+            general = imageops.resize(src, 2 * w, 2 * h, f, acc_init=acc, flags=L.FP_FAST | L.RESIZE_GENERAL).cpu().numpy()
+            assert np.allclose(got, want, rtol=1e-5, atol=1e-6), f"{f.name} {img.shape}: {np.abs(got - want).max()}"
+            assert np.allclose(general, want, rtol=1e-5, atol=1e-6)
+    # batch
+    imgs = np.stack([rand_image(rng, 200, 320, 4, np.float32) for _ in range(6)])
+    src = torch.from_numpy(imgs).to(cuda)
+    dst = torch.empty((6, 400, 640, 4), dtype=torch.float32, device=cuda)
+    L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, 320, 200, 4, L.F32, dst.data_ptr(), 0, 640, 400, 6, int(f), 1.0, L.FP_FAST, st))
+    got = dst.cpu().numpy()
+    for i in (0, 5):
+        assert np.allclose(got[i], o.resize(imgs[i], 640, 400, int(f)), rtol=1e-5, atol=1e-6)
+    # bands with odd seams
+    img = rand_image(rng, 900, 400, 4, np.float32)
+    want = o.resize(img, 800, 1800, int(f))
+    out = np.zeros_like(want)
+    for r0, rows in [(0, 601), (601, 598), (1199, 601)]:
+        s0, sn = ctypes.c_uint32(), ctypes.c_uint32()
+        L.check(lib.b200img_resize_band_src_rows(900, 1800, int(f), r0, rows, ctypes.byref(s0), ctypes.byref(sn)))
+        band = torch.from_numpy(img[s0.value:s0.value + sn.value].copy()).to(cuda)
+        d = torch.empty((rows, 800, 4), dtype=torch.float32, device=cuda)
+        L.check(lib.b200img_resize_band_dev(band.data_ptr(), s0.value, sn.value, 400, 900, 4, L.F32, d.data_ptr(), r0, rows,
+                                            800, 1800, int(f), 1.0, L.FP_FAST, st))
+        out[r0:r0 + rows] = d.cpu().numpy()
+    assert np.allclose(out, want, rtol=1e-5, atol=1e-6)
