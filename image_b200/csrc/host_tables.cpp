@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <limits>
 
 namespace b200 {
@@ -77,6 +78,37 @@ int resize_max_taps(int filter, uint32_t src_len, uint32_t dst_len) {
     return (int)rust_as<uint32_t>(ceilf(2.0f * (filter_support(filter) * sratio))) + 2;
 }
 
+// See AxisTable::fixed_R / up2.
+static void classify_axis(AxisTable &t, uint32_t src_len, uint32_t dst_len) {
+    t.fixed_R = 0; t.fixed_L0 = 0; t.up2 = false;
+    const int len = (int)src_len, NT = t.max_count;
+    if (dst_len >= 2 && src_len % dst_len == 0 && src_len / dst_len >= 2 && src_len / dst_len <= 64 && NT >= 2) {
+        const int R = (int)(src_len / dst_len);
+        const uint32_t mid = dst_len / 2;
+        bool ok = t.count[mid] == NT;
+        const int L0 = t.left[mid] - R * (int)mid;
+        const float *wm = &t.w[(size_t)mid * t.stride];
+        for (int k = 0; ok && k < NT / 2; ++k) ok = std::memcmp(&wm[k], &wm[NT - 1 - k], 4) == 0;
+        for (uint32_t o = 0; ok && o < dst_len; ++o) {
+            const int first = R * (int)o + L0, l = std::max(first, 0), r = std::min(first + NT, len);
+            ok = t.left[o] == l && t.count[o] == r - l &&
+                 (r - l != NT || std::memcmp(&t.w[(size_t)o * t.stride], wm, sizeof(float) * NT) == 0);
+        }
+        if (ok) { t.fixed_R = R; t.fixed_L0 = L0; }
+    }
+    if (dst_len == 2 * (uint64_t)src_len && NT == 7 && dst_len >= 32) {
+        const uint32_t mid = (dst_len / 2) & ~1u;
+        bool ok = t.count[mid] == 7 && t.count[mid + 1] == 7;
+        const float *w0 = &t.w[(size_t)mid * t.stride], *w1 = &t.w[(size_t)(mid + 1) * t.stride];
+        for (uint32_t o = 0; ok && o < dst_len; ++o) {
+            const int first = (int)(o >> 1) - 3, l = std::max(first, 0), r = std::min(first + 7, len);
+            ok = t.left[o] == l && t.count[o] == r - l &&
+                 (r - l != 7 || std::memcmp(&t.w[(size_t)o * t.stride], (o & 1) ? w1 : w0, sizeof(float) * 7) == 0);
+        }
+        t.up2 = ok;
+    }
+}
+
 void build_axis_table(int filter, uint32_t src_len, uint32_t dst_len, int axis, AxisTable &t) {
     const float ratio = (float)src_len / (float)dst_len;
     const float sratio = ratio < 1.0f ? 1.0f : ratio;
@@ -117,6 +149,7 @@ void build_axis_table(int filter, uint32_t src_len, uint32_t dst_len, int axis, 
         }
         for (int i = 0; i < t.count[o]; ++i) w[i] /= sum;
     }
+    classify_axis(t, src_len, dst_len);
 }
 
 // ---- Gaussian parameters ------------------------------------------------------

@@ -21,6 +21,13 @@ struct AxisTable {
     int max_count = 0;  // largest tap count actually used
     std::vector<int32_t> left, count;
     std::vector<float> w;  // dst_len x stride, zero padded
+    // Shape of the table, worked out once when it is built (the fixed-window kernels ask on every call):
+    // fixed_R > 0: a downscale by the integer fixed_R whose every window is [fixed_R o + fixed_L0, + max_count) cut to the
+    // image, the whole windows all carrying bitwise the weights of the middle one, and those symmetric;
+    // up2: a 2x upscale whose every window is [(o >> 1) - 3, + 7) cut to the image, the whole windows of each parity
+    // carrying bitwise the weights of the middle window of that parity.
+    int fixed_R = 0, fixed_L0 = 0;
+    bool up2 = false;
 };
 // axis 0: vertical_sample's rule; axis 1: horizontal_sample's rule.
 void build_axis_table(int filter, uint32_t src_len, uint32_t dst_len, int axis, AxisTable &t);

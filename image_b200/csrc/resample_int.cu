@@ -442,17 +442,6 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
 
 #undef RI_SYM
 
-// The window rule of one axis: every output o of [o0, o1) must tap exactly the samples of [R o + L0, R o + L0 + NT) that lie
-// inside the image, whole windows with bitwise the weights of `wmid`.
-bool axis_is_uniform(const AxisTable &t, int len, int R, int NT, int L0, uint32_t o0, uint32_t o1, const float *wmid) {
-    for (uint32_t o = o0; o < o1; ++o) {
-        const int first = R * (int)o + L0, l = std::max(first, 0), r = std::min(first + NT, len);
-        if (t.left[o] != l || t.count[o] != r - l) return false;
-        if (r - l == NT && std::memcmp(&t.w[(size_t)o * t.stride], wmid, sizeof(float) * NT) != 0) return false;
-    }
-    return true;
-}
-
 int round_up_i(int v, int m) { return (v + m - 1) / m * m; }
 
 struct IntGeo {
@@ -548,19 +537,14 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     const size_t gp = (size_t)w * C;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
     if ((uint64_t)w * C > (1u << 30) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
+    // both axes follow the fixed-window rule with symmetric weights (checked when the tables were built)
+    if (vt.fixed_R != R || ht.fixed_R != R) return 0;
     const int NT = vt.max_count;
     if (NT != ht.max_count || NT % R != 0 || NT > RI_MAX_TAPS) return 0;
     const int A = NT / R;
     if (A != 2 && A != 4 && A != 6) return 0;
-    // a whole window in the middle of each axis gives the rule and the weights
-    const uint32_t vm = nh / 2, hm = nw / 2;
-    if (vt.count[vm] != NT || ht.count[hm] != NT) return 0;
-    const int L0v = vt.left[vm] - R * (int)vm, L0h = ht.left[hm] - R * (int)hm;
-    const float *wvm = &vt.w[(size_t)vm * vt.stride], *whm = &ht.w[(size_t)hm * ht.stride];
-    for (int k = 0; k < NT / 2; ++k)  // the kernel keeps half of each (symmetric) weight vector
-        if (std::memcmp(&wvm[k], &wvm[NT - 1 - k], 4) != 0 || std::memcmp(&whm[k], &whm[NT - 1 - k], 4) != 0) return 0;
-    if (!axis_is_uniform(vt, (int)h, R, NT, L0v, dst_row0, dst_row0 + dst_rows, wvm)) return 0;
-    if (!axis_is_uniform(ht, (int)w, R, NT, L0h, 0, nw, whm)) return 0;
+    const int L0v = vt.fixed_L0, L0h = ht.fixed_L0;
+    const float *wvm = &vt.w[(size_t)(nh / 2) * vt.stride], *whm = &ht.w[(size_t)(nw / 2) * ht.stride];
 
     const int HR = C == 4 ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
     const int max_threads = C == 4 ? RI_THREADS_PX : RI_THREADS;

@@ -227,18 +227,6 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
     }
 }
 
-// one axis of the reference's tables: destination o = 2 m + ph taps [m - 3, m + 4) clipped to the image, whole windows with
-// bitwise the weights of that phase's middle window
-bool up2_axis_ok(const AxisTable &t, int len, const float *w0, const float *w1) {
-    const int n = (int)t.left.size();
-    for (int o = 0; o < n; ++o) {
-        const int first = (o >> 1) - U2_S, l = std::max(first, 0), r = std::min(first + U2_T, len);
-        if (t.left[o] != l || t.count[o] != r - l) return false;
-        if (r - l == U2_T && std::memcmp(&t.w[(size_t)o * t.stride], (o & 1) ? w1 : w0, sizeof(float) * U2_T) != 0) return false;
-    }
-    return true;
-}
-
 int up2_env_int(const char *name, int dflt) {
     const char *e = std::getenv(name);
     return e && *e ? std::atoi(e) : dflt;
@@ -257,12 +245,11 @@ int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
         dst_img_stride % 16 != 0)
         return 0;
     if (w > (1u << 28) || h > (1u << 28)) return 0;  // int arithmetic in the kernel
-    // whole windows in the middle of each axis give the two weight vectors
+    // both axes follow the 2x rule (checked when the tables were built); whole windows in the middle give the weight vectors
+    if (!vt.up2 || !ht.up2) return 0;
     const uint32_t vm = (nh / 2) & ~1u, hm = (nw / 2) & ~1u;
-    if (vt.count[vm] != U2_T || vt.count[vm + 1] != U2_T || ht.count[hm] != U2_T || ht.count[hm + 1] != U2_T) return 0;
     const float *wv0 = &vt.w[(size_t)vm * vt.stride], *wv1 = &vt.w[(size_t)(vm + 1) * vt.stride];
     const float *wh0 = &ht.w[(size_t)hm * ht.stride], *wh1 = &ht.w[(size_t)(hm + 1) * ht.stride];
-    if (!up2_axis_ok(vt, (int)h, wv0, wv1) || !up2_axis_ok(ht, (int)w, wh0, wh1)) return 0;
 
     Up2Args a;
     a.src = src; a.dst = dst; a.src_img_stride = src_img_stride; a.dst_img_stride = dst_img_stride;
