@@ -537,6 +537,7 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     const size_t gp = (size_t)w * C;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
     if ((uint64_t)w * C > (1u << 30) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
+    if (C == 4 && ((reinterpret_cast<uintptr_t>(dst) & 3) != 0 || dst_img_stride % 4 != 0)) return 0;  // the four-channel kernel stores whole pixels
     // both axes follow the fixed-window rule with symmetric weights (checked when the tables were built)
     if (vt.fixed_R != R || ht.fixed_R != R) return 0;
     const int NT = vt.max_count;

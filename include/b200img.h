@@ -84,10 +84,11 @@ typedef enum {
 /* Resampler only: use the tile kernel even where the column-streaming kernel (downscales of
  * u8 / u16 images) applies.  Same results; exists so that both kernels can be tested. */
 #define B200IMG_RESIZE_TILED 512
-/* Resampler only: do not use the kernel for u8 downscales by an even integer ratio (2x, 4x; fixed
- * window shape, one weight vector per axis, border windows renormalised after the sum) but the
- * table-driven kernels that serve every other size.  Both are within the FAST contract (+-1 LSB
- * of the reference); they may differ from each other by rounding.  For tests. */
+/* Resampler only: do not use the fixed-window kernels -- u8 downscales by an even integer ratio
+ * (2x, 4x) and exact 2x upscales of Rgba32F with a support-3 filter, where every window has the same
+ * shape, the weights are one or two vectors and border windows are renormalised after the sum -- but
+ * the table-driven kernels that serve every other size.  Both are within the FAST contract (+-1 LSB /
+ * 1e-5 relative of the reference); they may differ from each other by rounding.  For tests. */
 #define B200IMG_RESIZE_GENERAL 8192
 /* thumbnail only: evaluate every output pixel on its own (the kernel that serves upscales and
  * unaligned rows) even where the column-sum kernel applies.  Same results; for tests. */

@@ -106,3 +106,30 @@ def test_guard_bands_fused_kernels_and_bands(cuda, dtype, c):
             L.check(lib.b200img_fast_blur_band_src_rows(h, 2.0, r0, rows, C.byref(s0), C.byref(sn)))
             band = torch.from_numpy(np.ascontiguousarray(img[s0.value:s0.value + sn.value])).to(cuda)
             guarded(cuda, rows * w * c * es, lambda d: lib.b200img_fast_blur_band_dev(band.data_ptr(), s0.value, sn.value, w, h, c, dt, d, r0, rows, 2.0, st), off)
+
+
+def test_guard_bands_fixed_window_resamplers(cuda):
+    """The fixed-window resamplers (resample_int.cu, resample_up2.cu): batches large enough for them to be picked, ragged
+    last strips and bands, destinations that are and are not 16-byte aligned."""
+    import torch
+    lib = L.lib()
+    rng = np.random.default_rng(400)
+    st = torch.cuda.current_stream().cuda_stream
+    for c in (1, 3, 4):
+        for r, f in ((2, FilterType.Lanczos3), (4, FilterType.CatmullRom), (2, FilterType.Triangle)):
+            h, w, n = 92 * r, 372 * r, 12
+            imgs = np.stack([rand_image(rng, h, w, c, np.uint8) for _ in range(n)])
+            src = torch.from_numpy(imgs).to(cuda)
+            nw, nh = w // r, h // r
+            # (offsets that keep the kernel choice: the four-channel kernel wants whole-pixel alignment, and the guarded and the
+            # plain run are compared bit for bit)
+            for off in ((0, 4, 8) if c == 4 else (0, 1, 4)):
+                guarded(cuda, n * nw * nh * c, lambda d: lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, c, L.U8, d, 0, nw, nh, n, int(f),
+                                                                                      1.0, L.FP_FAST, st), off)
+    for f in (FilterType.Lanczos3, FilterType.Gaussian):
+        h, w, n = 150, 333, 5
+        imgs = np.stack([rand_image(rng, h, w, 4, np.float32) for _ in range(n)])
+        src = torch.from_numpy(imgs).to(cuda)
+        for off in (0, 16):
+            guarded(cuda, n * 4 * w * h * 16, lambda d: lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, L.F32, d, 0, 2 * w, 2 * h, n, int(f),
+                                                                                     1.0, L.FP_FAST, st), off)

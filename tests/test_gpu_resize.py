@@ -303,3 +303,57 @@ def test_resize_up2_rgba32f(cuda, f):
                                             800, 1800, int(f), 1.0, L.FP_FAST, st))
         out[r0:r0 + rows] = d.cpu().numpy()
     assert np.allclose(out, want, rtol=1e-5, atol=1e-6)
+
+
+def test_resize_fixed_window_fuzz(cuda):
+    """Random shapes through the fixed-window kernels (batches, so that they are picked): u8 downscales by 2 and 4 and
+    Rgba32F 2x upscales against the oracle on the first and last image."""
+    import torch
+    rng = np.random.default_rng(2024)
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    filters = [FilterType.Triangle, FilterType.CatmullRom, FilterType.Gaussian, FilterType.Lanczos3]
+    for it in range(10):
+        r = int(rng.choice([2, 4]))
+        c = int(rng.integers(1, 5))
+        nw, nh = int(rng.integers(40, 400)), int(rng.integers(30, 300))
+        while (nw * r * c) % 4:
+            nw += 1
+        f = filters[int(rng.integers(0, 4))]
+        n = int(rng.integers(6, 20))
+        acc = float(rng.choice([0.0, 1.0]))
+        imgs = rng.integers(0, 256, (n, nh * r, nw * r, c), dtype=np.uint8)
+        src = torch.from_numpy(imgs).to(cuda)
+        dst = torch.empty((n, nh, nw, c), dtype=torch.uint8, device=cuda)
+        L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, nw * r, nh * r, c, L.U8, dst.data_ptr(), 0, nw, nh, n, int(f), acc, L.FP_FAST, st))
+        got = dst.cpu().numpy().astype(np.int64)
+        for i in (0, n - 1):
+            want = o.resize(imgs[i], nw, nh, int(f), acc_init=acc).astype(np.int64)
+            assert np.abs(got[i] - want).max() <= 1, (it, r, c, nw, nh, f.name, n)
+    for it in range(4):
+        w, h = int(rng.integers(60, 500)), int(rng.integers(40, 400))
+        f = [FilterType.Lanczos3, FilterType.Gaussian][it & 1]
+        n = int(rng.integers(3, 8))
+        imgs = rng.random((n, h, w, 4), dtype=np.float32)
+        src = torch.from_numpy(imgs).to(cuda)
+        dst = torch.empty((n, 2 * h, 2 * w, 4), dtype=torch.float32, device=cuda)
+        L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, L.F32, dst.data_ptr(), 0, 2 * w, 2 * h, n, int(f), 1.0, L.FP_FAST, st))
+        got = dst.cpu().numpy()
+        for i in (0, n - 1):
+            want = o.resize(imgs[i], 2 * w, 2 * h, int(f))
+            assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6), (it, w, h, f.name)
+    # non-finite samples spread exactly as far as in the reference (the kernel multiplies the same seven taps per axis, the
+    # zero-weight end included, and pads with finite zeros): a batch large enough for the 2x kernel to be picked
+    imgs = rng.random((8, 160, 250, 4), dtype=np.float32) * 0.5 + 0.1
+    imgs[0, 80, 125] = np.inf
+    imgs[0, 3, 5, 1] = np.nan
+    imgs[7, 159, 249, 2] = np.nan
+    src = torch.from_numpy(imgs).to(cuda)
+    dst = torch.empty((8, 320, 500, 4), dtype=torch.float32, device=cuda)
+    L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, 250, 160, 4, L.F32, dst.data_ptr(), 0, 500, 320, 8, int(FilterType.Lanczos3), 0.0,
+                                         L.FP_FAST, st))
+    got = dst.cpu().numpy()
+    for i in (0, 7):
+        want = o.resize(imgs[i], 500, 320, int(FilterType.Lanczos3), acc_init=0.0)
+        assert np.array_equal(got[i] == 0, want == 0)          # NaN -> 0 in the f32 clamp (primitive_sealed.rs:127-137)
+        assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6)
