@@ -96,14 +96,15 @@ static void classify_axis(AxisTable &t, uint32_t src_len, uint32_t dst_len) {
         }
         if (ok) { t.fixed_R = R; t.fixed_L0 = L0; }
     }
-    if (dst_len == 2 * (uint64_t)src_len && NT == 7 && dst_len >= 32) {
+    if (dst_len == 2 * (uint64_t)src_len && (NT == 3 || NT == 5 || NT == 7) && dst_len >= 32) {
+        const int S = (NT - 1) / 2;
         const uint32_t mid = (dst_len / 2) & ~1u;
-        bool ok = t.count[mid] == 7 && t.count[mid + 1] == 7;
+        bool ok = t.count[mid] == NT && t.count[mid + 1] == NT;
         const float *w0 = &t.w[(size_t)mid * t.stride], *w1 = &t.w[(size_t)(mid + 1) * t.stride];
         for (uint32_t o = 0; ok && o < dst_len; ++o) {
-            const int first = (int)(o >> 1) - 3, l = std::max(first, 0), r = std::min(first + 7, len);
+            const int first = (int)(o >> 1) - S, l = std::max(first, 0), r = std::min(first + NT, len);
             ok = t.left[o] == l && t.count[o] == r - l &&
-                 (r - l != 7 || std::memcmp(&t.w[(size_t)o * t.stride], (o & 1) ? w1 : w0, sizeof(float) * 7) == 0);
+                 (r - l != NT || std::memcmp(&t.w[(size_t)o * t.stride], (o & 1) ? w1 : w0, sizeof(float) * NT) == 0);
         }
         t.up2 = ok;
     }

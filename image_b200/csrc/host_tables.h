@@ -24,8 +24,8 @@ struct AxisTable {
     // Shape of the table, worked out once when it is built (the fixed-window kernels ask on every call):
     // fixed_R > 0: a downscale by the integer fixed_R whose every window is [fixed_R o + fixed_L0, + max_count) cut to the
     // image, the whole windows all carrying bitwise the weights of the middle one, and those symmetric;
-    // up2: a 2x upscale whose every window is [(o >> 1) - 3, + 7) cut to the image, the whole windows of each parity
-    // carrying bitwise the weights of the middle window of that parity.
+    // up2: a 2x upscale whose every window is [(o >> 1) - S, + max_count) cut to the image (max_count = 2 S + 1 = 3, 5 or 7), the
+    // whole windows of each parity carrying bitwise the weights of the middle window of that parity.
     int fixed_R = 0, fixed_L0 = 0;
     bool up2 = false;
 };

@@ -1,6 +1,7 @@
-// resample_up2.cu -- the resampler for exact 2x upscales of four-channel f32 images with a support-3 filter
-// (Lanczos3, Gaussian) under B200IMG_FP_FAST: BASELINE config 4, the 32768^2 Rgba32F Lanczos3 upscale and its
-// row bands.
+// resample_up2.cu -- the resampler for exact 2x upscales of four-channel f32 images under B200IMG_FP_FAST:
+// BASELINE config 4, the 32768^2 Rgba32F Lanczos3 upscale and its row bands.  Written out below for the
+// support-3 filters (Lanczos3, Gaussian: seven taps); CatmullRom (five) and Triangle (three) are the same
+// kernel with a shorter window.
 //
 // At ratio 1/2 destination samples 2m and 2m+1 both tap the SAME seven source samples m-3 .. m+3
 // (vertical_sample / horizontal_sample, src/imageops/sample.rs:494-562, 217-340: centre m + 0.25 resp.
@@ -30,10 +31,8 @@
 namespace b200 {
 namespace {
 
-constexpr int U2_T = 7;          // taps
-constexpr int U2_S = 3;          // support
+constexpr int U2_MAXT = 7;       // taps, at most: 2 * support + 1 (the kernel is a template on the tap count: 3, 5 or 7)
 constexpr int U2_THREADS = 128;  // source pixel columns of a strip, halo included
-constexpr int U2_HR = 2 * U2_T;  // ring rows per buffer = destination rows per phase (seven source steps)
 
 struct Up2Args {
     const void *src;
@@ -45,23 +44,25 @@ struct Up2Args {
     int BANDS;          // source rows (= destination row pairs) per band, a multiple of 7
     int pitch;          // ring pixels per row (odd)
     float acc_init;
-    f32x2 wv[2][U2_T], wh[2][U2_T];  // (w, w) pairs; [phase][tap]
+    f32x2 wv[2][U2_MAXT], wh[2][U2_MAXT];  // (w, w) pairs; [phase][tap]
 };
 
 __device__ __forceinline__ float up2_lo(f32x2 v) { float a, b; unpack2(v, a, b); return a; }
 
-// 1 / (sum of the taps of the window [first, first + 7) that fall inside [0, len)); only for clipped windows
-__device__ __noinline__ float up2_border_scale(const f32x2 *w, int first, int len) {
-    const int k0 = max(0, -first), k1 = min(U2_T, len - first);
+// 1 / (sum of the taps of the window [first, first + T) that fall inside [0, len)); only for clipped windows
+__device__ __noinline__ float up2_border_scale(const f32x2 *w, int T, int first, int len) {
+    const int k0 = max(0, -first), k1 = min(T, len - first);
     float s = 0.0f;
 #pragma unroll 1
     for (int k = k0; k < k1; ++k) s += up2_lo(w[k]);
     return 1.0f / s;
 }
 
+template <int T>
 __global__ void __launch_bounds__(U2_THREADS, 3)
 resize_up2_kernel(const __grid_constant__ Up2Args a) {
-    constexpr int T = U2_T, S = U2_S, HR = U2_HR;
+    constexpr int S = (T - 1) / 2;   // support
+    constexpr int HR = 2 * T;        // ring rows per buffer = destination rows per phase (T source steps)
     extern __shared__ __align__(16) unsigned char smem[];
     ulonglong2 *s_ring = reinterpret_cast<ulonglong2 *>(smem);            // [2][HR][pitch] float4 pixels
     ulonglong2 *s_dump = s_ring + (size_t)2 * HR * a.pitch;               // one pixel
@@ -99,7 +100,7 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
         ++jnext;
         return v;
     };
-    ulonglong2 R[2 * T];   // circular window: row j0 + u lives in R[u % 14]
+    ulonglong2 R[2 * T];   // circular window: row j0 + u lives in R[u % (2 T)]
 #pragma unroll
     for (int k = 0; k < 2 * T; ++k) R[k] = make_ulonglong2(0ull, 0ull);
 #pragma unroll
@@ -110,7 +111,7 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
         const int n = i - HR, o = 2 * mA + n;          // local / global destination row
         const int first = (o >> 1) - S;                // its window (o >= 0 wherever it matters)
         float vs = 1.0f;
-        if (n >= 0 && n < 2 * nm && (first < 0 || first + T > (int)a.h)) vs = up2_border_scale(a.wv[o & 1], first, (int)a.h);
+        if (n >= 0 && n < 2 * nm && (first < 0 || first + T > (int)a.h)) vs = up2_border_scale(a.wv[o & 1], T, first, (int)a.h);
         s_vs[i] = vs;
     }
     __syncthreads();
@@ -157,7 +158,7 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
                 if (first < 0 || first + T > (int)a.w) {
 #pragma unroll
                     for (int ph = 0; ph < 2; ++ph) {
-                        const float hs = up2_border_scale(a.wh[ph], first, (int)a.w);
+                        const float hs = up2_border_scale(a.wh[ph], T, first, (int)a.w);
                         const f32x2 hs2 = pack2(hs, hs);
 #pragma unroll
                         for (int rr = 0; rr < 2; ++rr) {
@@ -240,7 +241,9 @@ int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
                    const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st) {
     if (dtype != B200IMG_F32 || C != 4) return 0;
     if (nw != 2 * w || nh != 2 * h || w < 16 || h < 16) return 0;
-    if (vt.max_count != U2_T || ht.max_count != U2_T) return 0;
+    const int T = vt.max_count;
+    if (T != ht.max_count || (T != 3 && T != 5 && T != 7)) return 0;
+    const int S = (T - 1) / 2;
     if ((reinterpret_cast<uintptr_t>(src) & 15) != 0 || (reinterpret_cast<uintptr_t>(dst) & 15) != 0 || src_img_stride % 16 != 0 ||
         dst_img_stride % 16 != 0)
         return 0;
@@ -256,40 +259,48 @@ int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     a.w = w; a.h = h; a.nw = nw; a.nh = nh; a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
     a.acc_init = acc_init;
     // strip width: the widest that the block covers with its halo, narrowed so that the strips are of equal width (multiples of 4)
-    int TWS = U2_THREADS - 2 * U2_S;
+    int TWS = U2_THREADS - 2 * S;
     const int strips0 = (int)((w + TWS - 1) / TWS);
     TWS = std::min(TWS, (int)(((w + strips0 - 1) / strips0 + 3) & ~3u));
     TWS = std::min(TWS, up2_env_int("B200IMG_U2_TWS", TWS)) & ~3;
     if (TWS < 4) return 0;
     a.TWS = TWS;
-    a.pitch = (4 * ((TWS + 3) / 4) + 2 * U2_S) | 1;
+    a.pitch = (4 * ((TWS + 3) / 4) + 2 * S) | 1;
     const int strips = (int)((w + TWS - 1) / TWS);
     const int pairs = (int)(((dst_row0 + dst_rows + 1) >> 1) - (dst_row0 >> 1));
     // rows per band: the job is bound by its stores and a CTA is a chain of short phases, so what matters is that the grid is
     // many times the resident CTAs (B200: 4096^2 -> 8192^2 0.34 ms with 21-row bands, 0.41 with 84; 8192^2 best at 63)
     int BANDS = 126;
-    while (BANDS > 3 * U2_T && (uint64_t)strips * ((pairs + BANDS - 1) / BANDS) * n_images < (uint64_t)ctx->sm_count * 48) BANDS -= U2_T;
+    BANDS = BANDS / T * T;
+    while (BANDS > 3 * T && (uint64_t)strips * ((pairs + BANDS - 1) / BANDS) * n_images < (uint64_t)ctx->sm_count * 48) BANDS -= T;
     {
         const int forced = up2_env_int("B200IMG_U2_BANDS", 0);
-        if (forced > 0) BANDS = std::min((forced + U2_T - 1) / U2_T * U2_T, 252);
+        if (forced > 0) BANDS = std::min((forced + T - 1) / T * T, 252 / T * T);
     }
     a.BANDS = BANDS;
     const int bands = (pairs + BANDS - 1) / BANDS;
     if (bands > 65535 || n_images > 65535) return 0;
     if ((uint64_t)strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;  // a small image: the tile kernels spread it better
     for (int ph = 0; ph < 2; ++ph)
-        for (int k = 0; k < U2_T; ++k) {
-            const float v = (ph ? wv1 : wv0)[k], hh = (ph ? wh1 : wh0)[k];
+        for (int k = 0; k < U2_MAXT; ++k) {
+            const float v = k < T ? (ph ? wv1 : wv0)[k] : 0.0f, hh = k < T ? (ph ? wh1 : wh0)[k] : 0.0f;
             uint32_t vb, hb;
             std::memcpy(&vb, &v, 4);
             std::memcpy(&hb, &hh, 4);
             a.wv[ph][k] = ((uint64_t)vb << 32) | vb;
             a.wh[ph][k] = ((uint64_t)hb << 32) | hb;
         }
-    const size_t smem = ((size_t)2 * U2_HR * a.pitch + 1) * 16 + (size_t)(2 * BANDS + 2 * U2_HR) * 4;
+    const int HR = 2 * T;
+    const size_t smem = ((size_t)2 * HR * a.pitch + 1) * 16 + (size_t)(2 * BANDS + 2 * HR) * 4;
     if (smem > ctx->smem_optin) return 0;
-    B200_CUDA(cudaFuncSetAttribute(resize_up2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    resize_up2_kernel<<<dim3((unsigned)strips, (unsigned)bands, n_images), U2_THREADS, smem, st>>>(a);
+    const dim3 grid((unsigned)strips, (unsigned)bands, n_images);
+#define U2_GO(TT)                                                                                                   \
+    {                                                                                                               \
+        B200_CUDA(cudaFuncSetAttribute(resize_up2_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        resize_up2_kernel<TT><<<grid, U2_THREADS, smem, st>>>(a);                                                   \
+    }
+    if (T == 7) U2_GO(7) else if (T == 5) U2_GO(5) else U2_GO(3)
+#undef U2_GO
     B200_CUDA(cudaGetLastError());
     return 1;
 }

@@ -264,7 +264,7 @@ def test_resize_integer_ratio_batch_and_bands(cuda):
     assert np.abs(out.astype(np.int64) - want).max() <= 1
 
 
-@pytest.mark.parametrize("f", [FilterType.Lanczos3, FilterType.Gaussian])
+@pytest.mark.parametrize("f", [FilterType.Triangle, FilterType.CatmullRom, FilterType.Lanczos3, FilterType.Gaussian])
 def test_resize_up2_rgba32f(cuda, f):
     """Exact 2x upscales of Rgba32F with a support-3 filter run the register-window kernel (resample_up2.cu): ragged strips
     and bands, both accumulator start values, a batch, and row bands that start and end on odd destination rows."""
@@ -332,7 +332,7 @@ def test_resize_fixed_window_fuzz(cuda):
             assert np.abs(got[i] - want).max() <= 1, (it, r, c, nw, nh, f.name, n)
     for it in range(4):
         w, h = int(rng.integers(60, 500)), int(rng.integers(40, 400))
-        f = [FilterType.Lanczos3, FilterType.Gaussian][it & 1]
+        f = [FilterType.Lanczos3, FilterType.Gaussian, FilterType.CatmullRom, FilterType.Triangle][it & 3]
         n = int(rng.integers(3, 8))
         imgs = rng.random((n, h, w, 4), dtype=np.float32)
         src = torch.from_numpy(imgs).to(cuda)
