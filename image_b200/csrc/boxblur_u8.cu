@@ -18,6 +18,7 @@
 #include "common.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 
 namespace b200 {
@@ -283,13 +284,24 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
 
     for (int ci = 0; ci < nchunks; ++ci) {
         // ---- (1) stage the chunk's source rows ----
-        for (int rr = warp; rr < F_CH; rr += F_WARPS) {
-            const int y = min(max(q0 + ci * F_CH + rr, 0), H - 1);
-            const uint32_t *gw = reinterpret_cast<const uint32_t *>(src + (size_t)y * g_pitch + (size_t)lo_px * C - a_g) + lane;
-            uint32_t d = s_in_u32 + (uint32_t)((rr * a.in_pitch + span_w0 + lane) * 4);
-#pragma unroll 4
-            for (int wi = lane; wi < span_words; wi += 32, gw += 32, d += 128)
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d), "l"(gw) : "memory");
+        {
+            // a warp stages rows warp, warp + 4, ...: the eight row pointers first, then one sweep over the span's words with
+            // the eight copies of a word column back to back (per-row address arithmetic once per chunk, not once per copy)
+            constexpr int RPW = F_CH / F_WARPS;
+            const uint8_t *grow[RPW];
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) {
+                const int y = min(max(q0 + ci * F_CH + warp + F_WARPS * i, 0), H - 1);
+                grow[i] = src + (size_t)y * g_pitch + (size_t)lo_px * C - a_g;
+            }
+            const uint32_t d0 = s_in_u32 + (uint32_t)((warp * a.in_pitch + span_w0) * 4);
+            const uint32_t dstep = (uint32_t)(F_WARPS * a.in_pitch * 4);
+#pragma unroll 1
+            for (int wi = lane; wi < span_words; wi += 32) {
+#pragma unroll
+                for (int i = 0; i < RPW; ++i)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d0 + i * dstep + 4u * wi), "l"(grow[i] + 4 * (size_t)wi) : "memory");
+            }
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
         if (n_in < sbytes) {   // an edge strip: replicate the span's first / last pixel outwards (each warp on its own rows)
@@ -444,9 +456,21 @@ int box_fused_u8(const uint8_t *src, uint8_t *dst, uint32_t w, uint32_t h, int C
     // bands: each primes its window with 2r + 1 extra rows.  A CTA runs its chunks as a chain of short phases, so the
     // GPU needs many of them in flight: about ten per SM (measured on B200: 8 x 4K Rgb8 0.96 ms with 2 bands, 0.73 ms
     // with 6), while a band stays at least four windows (and 64 rows) long so the priming stays a small share.
+    // Candidates up to ~20 CTAs per SM; among them the split whose last wave of CTAs is fullest, weighted by the share of a
+    // band's rows that are not priming (8 x 4K Rgb8: 6 bands = 1440 CTAs = 1.95 waves of 740: 0.67 ms; 7 bands = 2.27: 0.71).
     int bands = 1;
-    const int min_rows = std::max(64, 4 * (int)a.g.ks);
-    while ((uint64_t)strips * n_images * bands < 10ull * ctx->sm_count && (int)(h / (bands + 1)) >= min_rows) ++bands;
+    {
+        const int min_rows = std::max(64, 4 * (int)a.g.ks);
+        const uint64_t slots = (uint64_t)ctx->sm_count * std::max<size_t>(1, std::min<size_t>(16, (233472 - 1024) / (smem + 1024)));
+        double best = -1.0;
+        for (int b = 1; b <= 64 && (b == 1 || (int)(h / b) >= min_rows); ++b) {
+            const uint64_t total = (uint64_t)strips * n_images * b;
+            if (b > 1 && total > 20ull * ctx->sm_count && total > 2 * slots) break;
+            const double waves = (double)total / (double)slots, rows = (double)h / b;
+            const double score = waves / std::ceil(waves) * rows / (rows + a.g.ks) * (total >= slots ? 1.0 : 0.0 + waves);
+            if (score > best) { best = score; bands = b; }
+        }
+    }
     if (const char *e = getenv("B200IMG_BOX_BANDS")) { const int v = atoi(e); if (v >= 1) bands = std::min<int>(v, (int)h); }
     a.band_rows = (int)((h + bands - 1) / bands);
     a.bands = (int)((h + a.band_rows - 1) / a.band_rows);
