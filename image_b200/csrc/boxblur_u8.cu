@@ -282,27 +282,31 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
     int primed = 0;     // rows added so far (the window is full at ks)
     int out_left = b1 - b0;
 
-    for (int ci = 0; ci < nchunks; ++ci) {
-        // ---- (1) stage the chunk's source rows ----
-        {
-            // a warp stages rows warp, warp + 4, ...: the eight row pointers first, then one sweep over the span's words with
-            // the eight copies of a word column back to back (per-row address arithmetic once per chunk, not once per copy)
-            constexpr int RPW = F_CH / F_WARPS;
-            const uint8_t *grow[RPW];
+    // staging of chunk ci: asynchronous, in flight while the vertical pass of the chunk before it runs
+    auto stage = [&](int ci) {
+    {
+        // a warp stages rows warp, warp + 4, ...: the eight row pointers first, then one sweep over the span's words with
+        // the eight copies of a word column back to back (per-row address arithmetic once per chunk, not once per copy)
+        constexpr int RPW = F_CH / F_WARPS;
+        const uint8_t *grow[RPW];
 #pragma unroll
-            for (int i = 0; i < RPW; ++i) {
-                const int y = min(max(q0 + ci * F_CH + warp + F_WARPS * i, 0), H - 1);
-                grow[i] = src + (size_t)y * g_pitch + (size_t)lo_px * C - a_g;
-            }
-            const uint32_t d0 = s_in_u32 + (uint32_t)((warp * a.in_pitch + span_w0) * 4);
-            const uint32_t dstep = (uint32_t)(F_WARPS * a.in_pitch * 4);
-#pragma unroll 1
-            for (int wi = lane; wi < span_words; wi += 32) {
-#pragma unroll
-                for (int i = 0; i < RPW; ++i)
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d0 + i * dstep + 4u * wi), "l"(grow[i] + 4 * (size_t)wi) : "memory");
-            }
+        for (int i = 0; i < RPW; ++i) {
+            const int y = min(max(q0 + ci * F_CH + warp + F_WARPS * i, 0), H - 1);
+            grow[i] = src + (size_t)y * g_pitch + (size_t)lo_px * C - a_g;
         }
+        const uint32_t d0 = s_in_u32 + (uint32_t)((warp * a.in_pitch + span_w0) * 4);
+        const uint32_t dstep = (uint32_t)(F_WARPS * a.in_pitch * 4);
+#pragma unroll 1
+        for (int wi = lane; wi < span_words; wi += 32) {
+#pragma unroll
+            for (int i = 0; i < RPW; ++i)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d0 + i * dstep + 4u * wi), "l"(grow[i] + 4 * (size_t)wi) : "memory");
+        }
+    }
+    };
+    stage(0);
+    for (int ci = 0; ci < nchunks; ++ci) {
+        // ---- (1) the chunk's source rows have been requested (before the loop / during the previous chunk's vertical pass) ----
         asm volatile("cp.async.wait_all;" ::: "memory");
         if (n_in < sbytes) {   // an edge strip: replicate the span's first / last pixel outwards (each warp on its own rows)
             __syncwarp();
@@ -359,6 +363,7 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
             }
         }
         __syncthreads();
+        if (ci + 1 < nchunks) stage(ci + 1);   // the staging rows are free: the next chunk's copies fly during the vertical pass
 
         // ---- (3) vertical pass over the chunk's ring rows ----
         if (tid < owords) {
@@ -422,7 +427,8 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
                 if (rout >= rend) rout -= ring_span;
             }
         }
-        __syncthreads();   // the next chunk's staging and horizontal pass reuse s_in and the oldest ring rows
+        // (the barrier that follows the next chunk's staging wait also keeps its horizontal pass off the ring rows this
+        // vertical pass is still reading)
     }
 }
 
