@@ -39,6 +39,12 @@ struct U8Geom {
 __device__ __forceinline__ uint32_t even_lanes(uint32_t w) { return __byte_perm(w, 0, 0x4240); }  // [b0, 0, b2, 0]
 __device__ __forceinline__ uint32_t odd_lanes(uint32_t w) { return __byte_perm(w, 0, 0x4341); }   // [b1, 0, b3, 0]
 __device__ __forceinline__ uint32_t byte_of(uint32_t w, int j) { return __byte_perm(w, 0, 0x4440 + j); }
+// c + sum of (unsigned bytes of a) x (signed bytes of b): with b = 1 << 8k it adds byte k of a, with 0xFF << 8k it subtracts it
+__device__ __forceinline__ uint32_t dp4a_us(uint32_t a, int b, uint32_t c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"((int)c));
+    return (uint32_t)d;
+}
 
 // ---- vertical ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(V_THREADS)
@@ -181,7 +187,8 @@ box_h_u8_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, U8Ge
             for (int b = 0; b < 4 * C; ++b) {
                 const int c = b % C;
                 ob[b] = __umulhi(sum[c], g.recip);
-                sum[c] = sum[c] + byte_of(next[b / 4], b & 3) - byte_of(prev[b / 4], b & 3);
+                sum[c] = dp4a_us(next[b / 4], 1 << (8 * (b & 3)), sum[c]);
+                sum[c] = dp4a_us(prev[b / 4], (int)(0xFFu << (8 * (b & 3))), sum[c]);
             }
 #pragma unroll
             for (int k = 0; k < C; ++k)
@@ -351,7 +358,8 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
                     for (int b = 0; b < 4 * C; ++b) {
                         const int c = b % C;
                         ob[b] = __umulhi(sum[c], g.recip);
-                        sum[c] = sum[c] + byte_of(next[b / 4], b & 3) - byte_of(prev[b / 4], b & 3);
+                        sum[c] = dp4a_us(next[b / 4], 1 << (8 * (b & 3)), sum[c]);             // + byte (b & 3) of the incoming word
+                        sum[c] = dp4a_us(prev[b / 4], (int)(0xFFu << (8 * (b & 3))), sum[c]);  // - byte (b & 3) of the outgoing word
                     }
                     uint32_t *ow = out_row + (x * C) / 4;
 #pragma unroll
