@@ -222,7 +222,7 @@ int odd_words(int bytes) { return (((bytes + 3) / 4) | 1); }
 // streams down a band of rows in chunks of 32: (1) the chunk's source rows (+ r pixels either side) are
 // staged by asynchronous word copies; (2) the HORIZONTAL pass (lane = row, warp = chunk of F_XC pixels,
 // sliding sums as above) writes its quantised u8 rows into a ring of rows in shared memory; (3) the
-// VERTICAL pass (thread = one word column, the four running sums in two registers as 16-bit lanes) takes
+// VERTICAL pass (thread = one word column, four running sums updated with dp4a) takes
 // the chunk's rows from the ring one by one: emit a destination row, add the incoming row, subtract the
 // row 2r + 1 back.  Running sums persist from chunk to chunk, so inside a band nothing is computed twice;
 // a band primes its window with 2r + 1 rows.  The quantised store between the passes is the reference's
@@ -283,7 +283,7 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
     const int hchunks = (tw + F_XC - 1) / F_XC;
 
     // vertical state of this thread's word column
-    uint32_t se = g.bias | (g.bias << 16), so = se;
+    uint32_t sv[4] = {g.bias, g.bias, g.bias, g.bias};   // running sums of the word's four subpixels
     uint32_t *dcol = reinterpret_cast<uint32_t *>(dst + (size_t)b0 * g_pitch + (size_t)x0 * C) + tid;
     const size_t dwords = g_pitch / 4;
     int primed = 0;     // rows added so far (the window is full at ks)
@@ -387,16 +387,16 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
             const size_t ring_span = (size_t)a.ring_rows * a.ring_pitch;
             const int pitch = a.ring_pitch;
             auto emit = [&]() {
-                const uint32_t o0 = __umulhi(se & 0xffffu, g.recip), o2 = __umulhi(se >> 16, g.recip);
-                const uint32_t o1 = __umulhi(so & 0xffffu, g.recip), o3 = __umulhi(so >> 16, g.recip);
+                const uint32_t o0 = __umulhi(sv[0], g.recip), o1 = __umulhi(sv[1], g.recip);
+                const uint32_t o2 = __umulhi(sv[2], g.recip), o3 = __umulhi(sv[3], g.recip);
                 *dcol = __byte_perm(__byte_perm(o0, o1, 0x0040), __byte_perm(o2, o3, 0x0040), 0x5410);  // tw * C is a multiple of 4: whole words only
                 dcol += dwords;
             };
             // (a chunk's incoming rows never wrap: chunks and the ring are multiples of 32 rows)
             for (int k = 0; k < fill; ++k, ++primed) {   // filling the window (first chunk(s) of a band only)
                 const uint32_t vin = *rin;
-                se += even_lanes(vin);
-                so += odd_lanes(vin);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) sv[k] = dp4a_us(vin, 1 << (8 * k), sv[k]);
                 rin += pitch;
             }
             // steady state: every row emits a destination row (while the band has any left) and slides the window.
@@ -416,8 +416,11 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
 #pragma unroll
                     for (int u = 0; u < VU; ++u) {
                         emit();
-                        se = se + even_lanes(vin[u]) - even_lanes(vout[u]);
-                        so = so + odd_lanes(vin[u]) - odd_lanes(vout[u]);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            sv[k] = dp4a_us(vin[u], 1 << (8 * k), sv[k]);
+                            sv[k] = dp4a_us(vout[u], (int)(0xFFu << (8 * k)), sv[k]);
+                        }
                     }
                     rin += VU * pitch;
                     rout += VU * pitch;
@@ -425,8 +428,11 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
                 for (; i < seg; ++i) {
                     const uint32_t vin = *rin, vout = *rout;
                     if (i < e) emit();
-                    se = se + even_lanes(vin) - even_lanes(vout);
-                    so = so + odd_lanes(vin) - odd_lanes(vout);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        sv[k] = dp4a_us(vin, 1 << (8 * k), sv[k]);
+                        sv[k] = dp4a_us(vout, (int)(0xFFu << (8 * k)), sv[k]);
+                    }
                     rin += pitch;
                     rout += pitch;
                 }
