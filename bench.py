@@ -434,6 +434,28 @@ def multi_extras(torch, lib, L, dev, local, rank, world, dist, cpu_group, hbm, F
     del k4, o4
     torch.cuda.empty_cache()
 
+    # ---- K3 split: the 8192x8192 conversions / swizzle of BASELINE configs[2], each rank its contiguous range of pixels ----
+    npx = 8192 * 8192
+    rng_px = shard_range(npx, world, rank)
+    n_mine = len(rng_px)
+    g = torch.Generator(device=dev).manual_seed(2000 + rank)
+    a16 = torch.randint(0, 65536, (n_mine, 4), dtype=torch.int32, device=dev, generator=g).to(torch.uint16)
+    o8 = torch.empty((n_mine, 3), dtype=torch.uint8, device=dev)
+    bgra = torch.randint(0, 256, (n_mine, 4), dtype=torch.uint8, device=dev, generator=g)
+    k3 = {}
+    for name, fn, bytes_px in (
+            ("rgba16_to_rgb8", lambda: L.check(lib.b200img_convert_dev(a16.data_ptr(), L.U16, 4, o8.data_ptr(), L.U8, 3, n_mine, L.CAST, None, stream)), 11),
+            ("swizzle_bgra_inplace", lambda: L.check(lib.b200img_swizzle_02_dev(bgra.data_ptr(), L.U8, 4, n_mine * 4, stream)), 8)):
+        ms = max_over_ranks(time_device(fn, 3, 3, torch, (lambda: dist.barrier()) if dist else None))
+        k3[name] = {"ms": round(ms, 4), "MP/s": round(npx / 1e6 / (ms / 1e3), 1), "hbm_frac_per_gpu": round(npx * bytes_px / (ms / 1e3) / 1e9 / world / hbm, 4)}
+    if check and rank == 0:
+        sl = slice(n_mine - 4096, n_mine)
+        k3["parity"] = _parity(o8[sl].cpu().numpy(), oracle.convert(a16[sl].cpu().numpy(), 4, np.uint8, 3), 0)
+    k3["note"] = "whole job = one 8192x8192 image, each rank a contiguous range of its pixels (elementwise: no communication); time = max over ranks"
+    res[f"k3_8192_convert_split_{world}gpu"] = k3
+    del a16, o8, bgra
+    torch.cuda.empty_cache()
+
     # ---- K5: one side x side Rgba32F image -> 2x Lanczos3, `world` row bands, driven by rank 0 through the library ----
     if dist:
         dist.barrier(group=cpu_group)   # every rank has freed its K4 buffers; from here the other ranks leave their GPUs alone

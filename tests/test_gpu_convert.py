@@ -116,3 +116,31 @@ def test_from_raw_bgra_roundtrip(cuda):
     assert np.array_equal(img.data.reshape(-1), o.swizzle_02(raw, 4))
     assert np.array_equal(img.into_raw_bgra(), raw)
     assert ImageBuffer.from_raw_bgr(7, 5, raw[:10].copy()) is None
+
+
+def test_convert_and_swizzle_split_in_ranges(cuda):
+    """SURVEY 8(e), conversions / swizzle: elementwise, so an image may be split into any contiguous pixel ranges (one per GPU);
+    the pieces, converted separately (on every visible device in turn), are bit-identical to the whole."""
+    import torch
+    lib = L.lib()
+    rng = np.random.default_rng(5)
+    npx = 1 << 20
+    a = rng.integers(0, 65536, (npx, 4), dtype=np.uint16)
+    want = o.convert(a, 4, np.uint8, 3)
+    ndev = torch.cuda.device_count()
+    cuts = [0, 1, 333_333, 700_001, npx]
+    got = np.empty((npx, 3), np.uint8)
+    sw = np.empty((npx, 4), np.uint16)
+    for i in range(len(cuts) - 1):
+        dev = torch.device("cuda", i % ndev)
+        lo, hi = cuts[i], cuts[i + 1]
+        with torch.cuda.device(dev):
+            st = torch.cuda.current_stream().cuda_stream
+            src = torch.from_numpy(a[lo:hi].copy()).to(dev)
+            dst = torch.empty((hi - lo, 3), dtype=torch.uint8, device=dev)
+            L.check(lib.b200img_convert_dev(src.data_ptr(), L.U16, 4, dst.data_ptr(), L.U8, 3, hi - lo, L.CAST, None, st))
+            L.check(lib.b200img_swizzle_02_dev(src.data_ptr(), L.U16, 4, (hi - lo) * 4, st))
+            got[lo:hi] = dst.cpu().numpy()
+            sw[lo:hi] = src.cpu().numpy()
+    assert np.array_equal(got, want)
+    assert np.array_equal(sw, a[:, [2, 1, 0, 3]])
