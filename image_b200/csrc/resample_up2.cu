@@ -95,7 +95,8 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
     int jnext = j0;
     auto load_next = [&]() -> ulonglong2 {
         ulonglong2 v = make_ulonglong2(0ull, 0ull);
-        if (jnext >= 0 && jnext < (int)a.h && jnext < mA + nm + S) v = __ldg(reinterpret_cast<const ulonglong2 *>(gptr));
+        // (only rows that a pair of this band taps: a band's buffer holds nothing else, and the stream starts one row earlier)
+        if (jnext >= max(mA - S, 0) && jnext < min((int)a.h, mA + nm + S)) v = __ldg(reinterpret_cast<const ulonglong2 *>(gptr));
         gptr += gp;
         ++jnext;
         return v;
@@ -280,7 +281,9 @@ int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     a.BANDS = BANDS;
     const int bands = (pairs + BANDS - 1) / BANDS;
     if (bands > 65535 || n_images > 65535) return 0;
-    if ((uint64_t)strips * bands * n_images < (uint64_t)ctx->sm_count) return 0;  // a small image: the tile kernels spread it better
+    // small jobs: a CTA here is a chain of short phases with a window to fill and a ring to clear first, and the tile kernels
+    // spread a small image better (1080p -> 2160p 65 us here, 56 us there; 4096 x 2048 and up are faster here)
+    if ((uint64_t)w * pairs * n_images < (6u << 20) && !up2_env_int("B200IMG_U2_FORCE", 0)) return 0;
     for (int ph = 0; ph < 2; ++ph)
         for (int k = 0; k < U2_MAXT; ++k) {
             const float v = k < T ? (ph ? wv1 : wv0)[k] : 0.0f, hh = k < T ? (ph ? wh1 : wh0)[k] : 0.0f;

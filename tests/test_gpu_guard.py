@@ -108,10 +108,11 @@ def test_guard_bands_fused_kernels_and_bands(cuda, dtype, c):
             guarded(cuda, rows * w * c * es, lambda d: lib.b200img_fast_blur_band_dev(band.data_ptr(), s0.value, sn.value, w, h, c, dt, d, r0, rows, 2.0, st), off)
 
 
-def test_guard_bands_fixed_window_resamplers(cuda):
+def test_guard_bands_fixed_window_resamplers(cuda, monkeypatch):
     """The fixed-window resamplers (resample_int.cu, resample_up2.cu): batches large enough for them to be picked, ragged
     last strips and bands, destinations that are and are not 16-byte aligned."""
     import torch
+    monkeypatch.setenv("B200IMG_U2_FORCE", "1")   # the 2x kernel also on jobs smaller than the library would give it
     lib = L.lib()
     rng = np.random.default_rng(400)
     st = torch.cuda.current_stream().cuda_stream
