@@ -228,9 +228,12 @@ int odd_words(int bytes) { return (((bytes + 3) / 4) | 1); }
 // a band primes its window with 2r + 1 rows.  The quantised store between the passes is the reference's
 // (fast_blur.rs:36-71), so the result stays bit-identical.  Rows above / below the image are the first /
 // last row (fast_blur.rs:416-473): ring row q holds the horizontal pass of source row clamp(q).
-constexpr int F_XT = 128;      // strip width in pixels: small enough for four or five CTAs per SM, which overlap one another's staging waits
+// strip width in pixels: 128 for three and four channels (small enough for four or five CTAs per SM, which overlap one another's
+// staging waits); one and two channels take wider strips so that the vertical pass (a thread per 32-bit word column) has all
+// 128 threads busy and every warp gets several horizontal items per chunk
+__host__ __device__ constexpr int f_xt(int C) { return C == 1 ? 512 : C == 2 ? 256 : 128; }
 constexpr int F_XC = 32;       // pixels per horizontal-pass warp item
-constexpr int F_WARPS = F_XT / F_XC;
+constexpr int F_WARPS = 4;
 constexpr int F_THREADS = F_WARPS * 32;
 constexpr int F_CH = 32;       // rows per chunk = lanes of the horizontal pass
 
@@ -253,6 +256,7 @@ box_fused_u8_kernel(const FusedBoxArgs a) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const U8Geom &g = a.g;
     const int r = (int)g.r, W = (int)g.w, H = (int)g.h, ks = (int)g.ks;
+    constexpr int F_XT = f_xt(C);
     const int x0 = blockIdx.x * F_XT;
     const int band = blockIdx.y % a.bands;
     const size_t img = blockIdx.y / a.bands;
@@ -456,6 +460,7 @@ bool box_fused_u8_applies(uint32_t w, int C, uint32_t radius, const void *a, con
     const uint32_t ks = 2 * radius + 1;
     if (ks > 255 || ((size_t)w * C) % 4 != 0) return false;
     if (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 3) != 0) return false;
+    const int F_XT = f_xt(C);
     const int in_pitch = odd_words((F_XT + 2 * (int)radius + 1 + 8) * C + 8), ring_pitch = odd_words(F_XT * C + 4);
     const int ring_rows = (F_CH + (int)ks + F_CH - 1) / F_CH * F_CH;
     return ((size_t)F_CH * in_pitch + (size_t)ring_rows * ring_pitch) * 4 <= std::min<size_t>(ctx->smem_optin, 110 * 1024);  // at least two CTAs per SM
@@ -468,6 +473,7 @@ int box_fused_u8(const uint8_t *src, uint8_t *dst, uint32_t w, uint32_t h, int C
     a.g.w = w; a.g.h = h; a.g.r = radius; a.g.ks = 2 * radius + 1;
     a.g.recip = UINT32_MAX / a.g.ks + 1u;
     a.g.bias = a.g.ks / 2;
+    const int F_XT = f_xt(C);
     a.in_pitch = odd_words((F_XT + 2 * (int)radius + 1 + 8) * C + 8);  // slack: the last 4-pixel step reads up to C + 1 words past the last incoming pixel
     a.ring_pitch = odd_words(F_XT * C + 4);
     a.ring_rows = (F_CH + (int)a.g.ks + F_CH - 1) / F_CH * F_CH;
