@@ -464,10 +464,99 @@ def multi_extras(torch, lib, L, dev, local, rank, world, dist, cpu_group, hbm, F
             res.update(k5_bands(torch, lib, L, world, hbm, FilterType, plan_bands, check, k5_side))
         except Exception as e:  # noqa: BLE001 -- the main line must still be printed
             res["k5_bands_error"] = repr(e)[:300]
+        try:
+            res.update(blur_bands(torch, lib, L, world, hbm, plan_bands, check))
+        except Exception as e:  # noqa: BLE001
+            res["blur_bands_error"] = repr(e)[:300]
     if dist:
         dist.barrier(group=cpu_group)
     return res
 
+
+
+def blur_bands(torch, lib, L, n_dev, hbm, plan_bands, check, side=16384):
+    """One side x side Rgb8 image, Gaussian blur sigma = 10 (f32 engine) and fast_blur sigma = 10, split into `n_dev` row bands
+    inside the library: rank 0 drives every device, ghost rows (32 / 29 per seam side) by cudaMemcpyPeerAsync."""
+    from image_b200 import GaussianBlurParameters
+    h = w = side
+    p = GaussianBlurParameters.new_from_sigma(10.0)
+    out = {}
+    for op in ("gaussian", "fast_blur"):
+        bands = plan_bands(op, h, n_dev, params=p, sigma=10.0)
+        keep, streams = [], []
+        for k in range(n_dev):
+            b = bands[k]
+            d = torch.device("cuda", k)
+            with torch.cuda.device(d):
+                gk = torch.Generator(device=d).manual_seed(11 + k)
+                srcb = torch.full((b.src_rows, w, 3), 0xAB, dtype=torch.uint8, device=d)   # ghost rows start as 0xAB
+                o0 = b.own_row0 - b.src_row0
+                srcb[o0:o0 + b.own_rows] = torch.randint(0, 256, (b.own_rows, w, 3), dtype=torch.uint8, device=d, generator=gk)
+                dstb = torch.empty((b.dst_rows, w, 3), dtype=torch.uint8, device=d)
+                st = torch.cuda.Stream(device=d)
+            b.device, b.d_src, b.d_dst = k, srcb.data_ptr(), dstb.data_ptr()
+            keep.append((srcb, dstb))
+            streams.append(st)
+        sarr = (C.c_void_p * n_dev)(*[s.cuda_stream for s in streams])
+        for k in range(n_dev):
+            torch.cuda.synchronize(k)
+        if op == "gaussian":
+            call = lambda: L.check(lib.b200img_gaussian_blur_bands(bands, n_dev, w, h, 3, L.U8, C.byref(p.raw), L.BLUR_GENERIC, L.FP_FAST, sarr))
+        else:
+            call = lambda: L.check(lib.b200img_fast_blur_bands(bands, n_dev, w, h, 3, L.U8, 10.0, sarr))
+        for _ in range(2):
+            call()
+        for s_ in streams:
+            s_.synchronize()
+        steps = 3
+        ev = []
+        for k in range(n_dev):
+            with torch.cuda.device(k):
+                ev.append((torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
+        for k in range(n_dev):
+            ev[k][0].record(streams[k])
+        for _ in range(steps):
+            call()
+        for k in range(n_dev):
+            ev[k][1].record(streams[k])
+        for s_ in streams:
+            s_.synchronize()
+        ms = max(ev[k][0].elapsed_time(ev[k][1]) for k in range(n_dev)) / steps
+        entry = {"side": side, "ms": round(ms, 4), "MP/s": round(h * w / 1e6 / (ms / 1e3), 1),
+                 "hbm_frac_per_gpu": round(2 * h * w * 3 / (ms / 1e3) / 1e9 / n_dev / hbm, 4),
+                 "note": "one process drives every device; ghost rows by cudaMemcpyPeerAsync inside the library; ms = max over devices of "
+                         "CUDA-event time on each band's stream"}
+        if check:
+            import oracle
+            seam = bands[1].dst_row0 if n_dev > 1 else h // 2
+            halo = 40
+            lo, hi = seam - 48 - halo, seam + 48 + halo
+
+            def rows_of(which, r0, r1):   # own source rows / destination rows from whichever band holds them
+                res_ = np.empty((r1 - r0, w, 3), np.uint8)
+                for k in range(n_dev):
+                    b = bands[k]
+                    if which == 0:
+                        a0, a1, base, t_ = b.own_row0, b.own_row0 + b.own_rows, b.src_row0, keep[k][0]
+                    else:
+                        a0, a1, base, t_ = b.dst_row0, b.dst_row0 + b.dst_rows, b.dst_row0, keep[k][1]
+                    x0, x1 = max(r0, a0), min(r1, a1)
+                    if x0 < x1:
+                        res_[x0 - r0:x1 - r0] = t_[x0 - base:x1 - base].cpu().numpy()
+                return res_
+            src_rows = rows_of(0, lo, hi)[:, :4096]      # a 4096-column window is enough for the row pass's 32-pixel reach ...
+            got = rows_of(1, seam - 48, seam + 48)[:, 64:4096 - 64]   # ... away from the window's own edges
+            if op == "gaussian":
+                want = oracle.gaussian_blur(src_rows, oracle.gauss_params_from_sigma(10.0), "generic", chunked=True)
+            else:
+                want = oracle.fast_blur(src_rows, 10.0)
+            entry["parity"] = _parity(got, want[halo:halo + 96, 64:4096 - 64], None if op == "gaussian" else 0)
+        out[f"{op}_bands_sigma10_rgb8_{side}_{n_dev}gpu"] = entry
+        del keep
+        for k in range(n_dev):
+            with torch.cuda.device(k):
+                torch.cuda.empty_cache()
+    return out
 
 def k5_bands(torch, lib, L, n_dev, hbm, FilterType, plan_bands, check, side):
     # the largest power-of-two side (<= 32768) whose bands fit the devices' free memory with room to spare
