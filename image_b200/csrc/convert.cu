@@ -348,12 +348,116 @@ int convert_dev(const void *src, int sd, int cin, void *dst, int dd, int cout, s
     return fail(B200IMG_ERR_BAD_ARG, "convert: bad src_dtype");
 }
 
+// Four-channel swizzle in place (bgra_to_rgba, src/primitive_sealed.rs:34-67): a pixel never straddles a 16-byte vector, so
+// nothing needs staging: 128-bit loads (four per thread in flight), a byte / lane permute in registers, 128-bit stores to the
+// same addresses.  (The tile kernel above moves the same bytes through shared memory with one tile of prefetch: 71 % of the
+// HBM rate on 8192^2 BGRA8 against this kernel's figure in DESIGN.md.)
+template <int ESZ> __device__ __forceinline__ uint4 swizzle4_vec(uint4 v) {
+    if constexpr (ESZ == 1) {          // four pixels: bytes (b, g, r, a) -> (r, g, b, a) in every word
+        v.x = __byte_perm(v.x, 0, 0x3012); v.y = __byte_perm(v.y, 0, 0x3012);
+        v.z = __byte_perm(v.z, 0, 0x3012); v.w = __byte_perm(v.w, 0, 0x3012);
+        return v;
+    } else if constexpr (ESZ == 2) {   // two pixels: halves (c0 c1 | c2 c3) -> (c2 c1 | c0 c3)
+        return make_uint4(__byte_perm(v.x, v.y, 0x3254), __byte_perm(v.x, v.y, 0x7610), __byte_perm(v.z, v.w, 0x3254), __byte_perm(v.z, v.w, 0x7610));
+    } else {                           // one pixel
+        return make_uint4(v.z, v.y, v.x, v.w);
+    }
+}
+
+template <int ESZ>
+__global__ void __launch_bounds__(256)
+swizzle4_kernel(uint4 *buf, size_t nvec) {
+    const size_t stride = (size_t)gridDim.x * 256;
+    size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        const uint4 a = buf[i], b = buf[i + stride], c = buf[i + 2 * stride], d = buf[i + 3 * stride];
+        buf[i] = swizzle4_vec<ESZ>(a);
+        buf[i + stride] = swizzle4_vec<ESZ>(b);
+        buf[i + 2 * stride] = swizzle4_vec<ESZ>(c);
+        buf[i + 3 * stride] = swizzle4_vec<ESZ>(d);
+    }
+    for (; i < nvec; i += stride) buf[i] = swizzle4_vec<ESZ>(buf[i]);
+}
+
+// Three channels: 48 bytes (three vectors) hold a whole number of pixels for every element size (16 / 8 / 4 pixels), so a
+// thread takes three consecutive vectors and permutes inside them; the byte patterns repeat every three words.
+template <int ESZ> __device__ __forceinline__ void swizzle3_words(uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    if constexpr (ESZ == 1) {          // bytes b g r b | g r b g | r b g r  ->  r g b r | g b r g | b r g b
+        const uint32_t n0 = __byte_perm(w0, w1, 0x5012);
+        const uint32_t t = __byte_perm(w0, w1, 0x7034);
+        const uint32_t n1 = __byte_perm(t, w2, 0x3410);
+        const uint32_t n2 = __byte_perm(w1, w2, 0x5672);
+        w0 = n0; w1 = n1; w2 = n2;
+    } else if constexpr (ESZ == 2) {   // halves c0 c1 | c2 c0' | c1' c2'  ->  c2 c1 | c0 c2' | c1' c0'
+        const uint32_t n0 = __byte_perm(w0, w1, 0x3254), n1 = __byte_perm(w0, w2, 0x7610), n2 = __byte_perm(w2, w1, 0x7610);
+        w0 = n0; w1 = n1; w2 = n2;
+    } else {
+        const uint32_t t = w0; w0 = w2; w2 = t;
+    }
+}
+
+template <int ESZ>
+__global__ void __launch_bounds__(256)
+swizzle3_kernel(uint4 *buf, size_t nchunks) {   // a chunk = three vectors
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < nchunks; i += stride) {
+        uint4 a = buf[3 * i], b = buf[3 * i + 1], c = buf[3 * i + 2];
+        swizzle3_words<ESZ>(a.x, a.y, a.z);
+        swizzle3_words<ESZ>(a.w, b.x, b.y);
+        swizzle3_words<ESZ>(b.z, b.w, c.x);
+        swizzle3_words<ESZ>(c.y, c.z, c.w);
+        buf[3 * i] = a; buf[3 * i + 1] = b; buf[3 * i + 2] = c;
+    }
+}
+
+template <int ESZ>
+int swizzle3_launch(void *buf, size_t nchunks, cudaStream_t st) {
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    if (nchunks == 0) return B200IMG_OK;
+    const unsigned grid = (unsigned)std::min<size_t>((nchunks + 255) / 256, (size_t)ctx->sm_count * 16);
+    swizzle3_kernel<ESZ><<<grid, 256, 0, st>>>(reinterpret_cast<uint4 *>(buf), nchunks);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
+template <int ESZ>
+int swizzle4_launch(void *buf, size_t npixels, cudaStream_t st) {
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    constexpr size_t PX_PER_VEC = 16 / (4 * ESZ);
+    const size_t nvec = npixels / PX_PER_VEC;     // (npixels % PX_PER_VEC pixels are left to the caller)
+    if (nvec == 0) return B200IMG_OK;
+    const size_t want = (nvec + 4 * 256 - 1) / (4 * 256);
+    const unsigned grid = (unsigned)std::min<size_t>(want, (size_t)ctx->sm_count * 8);
+    swizzle4_kernel<ESZ><<<grid, 256, 0, st>>>(reinterpret_cast<uint4 *>(buf), nvec);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
 int swizzle_dev(void *buf, int dtype, int channels, size_t nsub, cudaStream_t st) {
     if (channels != 3 && channels != 4) return fail(B200IMG_ERR_BAD_ARG, "swizzle: channels must be 3 or 4");
-    const size_t n = nsub / (size_t)channels;  // full chunks only (as_chunks_mut)
+    size_t n = nsub / (size_t)channels;  // full chunks only (as_chunks_mut)
     if (n == 0) return B200IMG_OK;
     if (!buf) return fail(B200IMG_ERR_BAD_ARG, "swizzle: null buffer");
     Coefs k = {0, 0, 0, 0};
+    if (channels == 4 && (reinterpret_cast<uintptr_t>(buf) & 15) == 0 && n >= 4096) {
+        // whole 16-byte vectors by the direct kernel, the last one to three pixels (u8 / u16 only) by the tile kernel
+        const size_t esz = dtype_size(dtype), per_vec = 16 / (4 * esz), body = n / per_vec * per_vec;
+        int rc = dtype == B200IMG_U8 ? swizzle4_launch<1>(buf, body, st) : dtype == B200IMG_U16 ? swizzle4_launch<2>(buf, body, st)
+                                                                                                  : swizzle4_launch<4>(buf, body, st);
+        if (rc || body == n) return rc;
+        buf = reinterpret_cast<unsigned char *>(buf) + body * 4 * esz;
+        n -= body;
+    }
+    if (channels == 3 && (reinterpret_cast<uintptr_t>(buf) & 15) == 0 && n >= 4096) {
+        const size_t esz = dtype_size(dtype), per_chunk = 48 / (3 * esz), chunks = n / per_chunk, body = chunks * per_chunk;
+        int rc = dtype == B200IMG_U8 ? swizzle3_launch<1>(buf, chunks, st) : dtype == B200IMG_U16 ? swizzle3_launch<2>(buf, chunks, st)
+                                                                                                  : swizzle3_launch<4>(buf, chunks, st);
+        if (rc || body == n) return rc;
+        buf = reinterpret_cast<unsigned char *>(buf) + body * 3 * esz;
+        n -= body;
+    }
 #define SWZ(T, C) launch<T, T, C, C, MODE_SWIZZLE>(buf, buf, n, k, st)
     switch (dtype) {
         case B200IMG_U8: return channels == 3 ? SWZ(uint8_t, 3) : SWZ(uint8_t, 4);

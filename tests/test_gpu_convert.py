@@ -86,7 +86,7 @@ def test_k3_shapes_bit_exact(cuda):
 @pytest.mark.parametrize("ch", [3, 4])
 def test_swizzle(cuda, dtype, ch):
     import torch
-    for n in (0, 1, ch - 1, ch, 4 * 1024 * ch, 4 * 1024 * ch + ch - 1, 100003):
+    for n in (0, 1, ch - 1, ch, 4 * 1024 * ch, 4 * 1024 * ch + ch - 1, 4 * 1024 * ch + 5 * ch + 1, 100003, 1000003):
         a = _special(dtype, n) if n else np.zeros(0, dtype)
         dev = torch.from_numpy(a.copy()).to(cuda)
         imageops.swizzle_02(dev, ch)
