@@ -271,8 +271,65 @@ convert_kernel(const S *src, D *dst, size_t npixels, Coefs k, int bulk_ok) {
     if (tid == 0) bulk_wait<0>();
 }
 
+// The same conversion straight from / to global memory: a warp takes 128 consecutive pixels per trip, lane L the pixels
+// L, L + 32, L + 64, L + 96 (so every access of the warp is one contiguous run), all loads of a trip first.  Pixels of 2, 4, 8
+// or 16 bytes move as one access; 3-, 6- and 12-byte pixels element by element (the three accesses of a warp cover the same
+// lines, L1 and L2 merge them).
+template <typename S, typename D, int CIN, int COUT, int MODE>
+__global__ void __launch_bounds__(256)
+convert_direct_kernel(const S *__restrict__ src, D *__restrict__ dst, size_t npixels, Coefs k) {
+    const int lane = threadIdx.x & 31;
+    const size_t warps = (size_t)gridDim.x * 8;
+    for (size_t base = ((size_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 128; base < npixels; base += warps * 128) {
+        S sv[4][CIN];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const size_t p = base + lane + 32 * j;
+            if (p < npixels) lds_px<S, CIN>(src + p * CIN, sv[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const size_t p = base + lane + 32 * j;
+            if (p < npixels) {
+                D dv[COUT];
+                convert_px<S, D, CIN, COUT, MODE>(sv[j], dv, k);
+                sts_px<D, COUT>(dst + p * COUT, dv);
+            }
+        }
+    }
+}
+
+template <typename S, typename D, int CIN, int COUT, int MODE>
+int launch_direct(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStream_t stream) {
+    DeviceCtx *ctx = current_ctx();
+    if (!ctx) return B200IMG_ERR_CUDA;
+    const size_t want = (npixels + 1023) / 1024;
+    const unsigned grid = (unsigned)std::min<size_t>(want, (size_t)ctx->sm_count * 8);
+    convert_direct_kernel<S, D, CIN, COUT, MODE><<<grid, 256, 0, stream>>>((const S *)src, (D *)dst, npixels, k);
+    B200_CUDA(cudaGetLastError());
+    return B200IMG_OK;
+}
+
 template <typename S, typename D, int CIN, int COUT, int MODE>
 int launch(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStream_t stream) {
+    {
+        // Which kernel: the direct one wherever the source pixel is one access (1 / 2 / 4 / 8 / 16 bytes, or f32 elements) or the
+        // destination pixel is narrow; sub-word source pixels (Rgb8, Rgb16, La16 ...) feeding wide destination pixels stay on the
+        // tile kernel, whose bulk copies read them better than byte loads do (8192^2, share of the HBM rate, tile / direct:
+        // Rgba16 -> Rgb8 0.80 / 0.98, Rgba8 -> Rgb8 0.60 / 0.88, Rgba32F -> Rgba8 0.91 / 0.94, Luma8 -> Rgba8 0.44 / 0.66,
+        // Rgb8 -> Rgba32F 0.82 / 0.81, Rgb8 -> Rgba8 0.62 / 0.57, Rgb16 -> Rgba16 0.80 / 0.78; tools/time_convert.py).
+        // B200IMG_CONVERT_KERNEL = tile | direct forces one (tests run both); the direct kernel's vector accesses need
+        // pixel-aligned buffers.
+        constexpr size_t BI = sizeof(S) * CIN, BO = sizeof(D) * COUT;
+        constexpr bool VI = BI == 16 || BI == 8 || BI == 4 || BI == 2 || BI == 1, VO = BO == 16 || BO == 8 || BO == 4 || BO == 2 || BO == 1;
+        constexpr size_t AI = VI ? BI : sizeof(S), AO = VO ? BO : sizeof(D);
+        const char *force = getenv("B200IMG_CONVERT_KERNEL");
+        bool direct = VI || sizeof(S) == 4 || BO < 4;
+        if (force && force[0] == 't') direct = false;
+        if (force && force[0] == 'd') direct = true;
+        if (direct && MODE != MODE_SWIZZLE && reinterpret_cast<uintptr_t>(src) % AI == 0 && reinterpret_cast<uintptr_t>(dst) % AO == 0)
+            return launch_direct<S, D, CIN, COUT, MODE>(src, dst, npixels, k, stream);
+    }
     DeviceCtx *ctx = current_ctx();
     if (!ctx) return B200IMG_ERR_CUDA;
     auto kern = convert_kernel<S, D, CIN, COUT, MODE>;

@@ -26,10 +26,13 @@ def _special(dtype, n):
     return lcg_array(0x1234ABCD, n, dtype)
 
 
+@pytest.mark.parametrize("kernel", ["tile", "direct"])
 @pytest.mark.parametrize("mode", [L.CAST, L.CONVERT])
 @pytest.mark.parametrize("sd,dd", list(itertools.product(DT, DT)))
-def test_convert_all_layouts(cuda, sd, dd, mode):
+def test_convert_all_layouts(cuda, sd, dd, mode, kernel, monkeypatch):
+    """Every layout pair through BOTH conversion kernels (the library picks one per pair; B200IMG_CONVERT_KERNEL forces it)."""
     import torch
+    monkeypatch.setenv("B200IMG_CONVERT_KERNEL", kernel)
     npx = 5000 + 37  # several tiles plus a ragged tail
     for sc, dc in itertools.product([1, 2, 3, 4], [1, 2, 3, 4]):
         src = _special(sd, npx * sc).reshape(npx, sc)
