@@ -299,6 +299,57 @@ convert_direct_kernel(const S *__restrict__ src, D *__restrict__ dst, size_t npi
     }
 }
 
+// Rgb8 sources with narrow destination pixels (to_luma8, to_luma_alpha8, to_rgba8, Luma16 / La8 ...): byte loads of 3-byte
+// pixels are what holds the two kernels above back on these, so a thread takes 48 bytes = 16 pixels as three 128-bit loads,
+// unpacks them in registers and writes its 16 destination pixels (1, 2 or 4 bytes each) as one, two or four 128-bit stores.
+template <typename D, int COUT> __device__ __forceinline__ uint32_t px_bits(const D (&d)[COUT]) {
+    uint32_t v = 0;
+    if constexpr (sizeof(D) == 4) {
+        v = __float_as_uint((float)d[0]);
+    } else {
+#pragma unroll
+        for (int c = 0; c < COUT; ++c) v |= (uint32_t)d[c] << (8 * sizeof(D) * c);
+    }
+    return v;
+}
+
+template <typename D, int COUT, int MODE>
+__global__ void __launch_bounds__(256)
+convert_rgb8_chunks_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, size_t nchunks, Coefs k) {
+    constexpr int BO = sizeof(D) * COUT;   // 1, 2 or 4
+    const size_t stride = (size_t)gridDim.x * 256;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < nchunks; i += stride) {
+        const uint4 a = src[3 * i], b = src[3 * i + 1], c = src[3 * i + 2];
+        const uint32_t w[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+        uint32_t o[16];
+#pragma unroll
+        for (int p = 0; p < 16; ++p) {
+            uint8_t sv[3];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                const int byte = 3 * p + ch;
+                sv[ch] = (uint8_t)(w[byte >> 2] >> (8 * (byte & 3)));
+            }
+            D dv[COUT];
+            convert_px<uint8_t, D, 3, COUT, MODE>(sv, dv, k);
+            o[p] = px_bits<D, COUT>(dv);
+        }
+        uint4 *out = dst + (size_t)BO * i;
+        if constexpr (BO == 4) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) out[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        } else if constexpr (BO == 2) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                out[j] = make_uint4(o[8 * j] | o[8 * j + 1] << 16, o[8 * j + 2] | o[8 * j + 3] << 16, o[8 * j + 4] | o[8 * j + 5] << 16,
+                                    o[8 * j + 6] | o[8 * j + 7] << 16);
+        } else {
+            out[0] = make_uint4(o[0] | o[1] << 8 | o[2] << 16 | o[3] << 24, o[4] | o[5] << 8 | o[6] << 16 | o[7] << 24,
+                                o[8] | o[9] << 8 | o[10] << 16 | o[11] << 24, o[12] | o[13] << 8 | o[14] << 16 | o[15] << 24);
+        }
+    }
+}
+
 template <typename S, typename D, int CIN, int COUT, int MODE>
 int launch_direct(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStream_t stream) {
     DeviceCtx *ctx = current_ctx();
@@ -324,6 +375,21 @@ int launch(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStrea
         constexpr bool VI = BI == 16 || BI == 8 || BI == 4 || BI == 2 || BI == 1, VO = BO == 16 || BO == 8 || BO == 4 || BO == 2 || BO == 1;
         constexpr size_t AI = VI ? BI : sizeof(S), AO = VO ? BO : sizeof(D);
         const char *force = getenv("B200IMG_CONVERT_KERNEL");
+        if constexpr (sizeof(S) == 1 && CIN == 3 && MODE != MODE_SWIZZLE && (BO == 1 || BO == 2 || BO == 4)) {
+            // Rgb8 -> 1 / 2 / 4-byte pixels: whole 16-pixel chunks by the chunk kernel, the last pixels by the kernels below
+            if (!force && npixels >= 4096 && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+                DeviceCtx *ctx = current_ctx();
+                if (!ctx) return B200IMG_ERR_CUDA;
+                const size_t chunks = npixels / 16;
+                const unsigned grid = (unsigned)std::min<size_t>((chunks + 255) / 256, (size_t)ctx->sm_count * 16);
+                convert_rgb8_chunks_kernel<D, COUT, MODE><<<grid, 256, 0, stream>>>((const uint4 *)src, (uint4 *)dst, chunks, k);
+                B200_CUDA(cudaGetLastError());
+                if (chunks * 16 == npixels) return B200IMG_OK;
+                src = reinterpret_cast<const unsigned char *>(src) + chunks * 48;
+                dst = reinterpret_cast<unsigned char *>(dst) + chunks * 16 * BO;
+                npixels -= chunks * 16;
+            }
+        }
         bool direct = VI || sizeof(S) == 4 || BO < 4;
         if (force && force[0] == 't') direct = false;
         if (force && force[0] == 'd') direct = true;

@@ -26,13 +26,16 @@ def _special(dtype, n):
     return lcg_array(0x1234ABCD, n, dtype)
 
 
-@pytest.mark.parametrize("kernel", ["tile", "direct"])
+@pytest.mark.parametrize("kernel", ["tile", "direct", "auto"])
 @pytest.mark.parametrize("mode", [L.CAST, L.CONVERT])
 @pytest.mark.parametrize("sd,dd", list(itertools.product(DT, DT)))
 def test_convert_all_layouts(cuda, sd, dd, mode, kernel, monkeypatch):
-    """Every layout pair through BOTH conversion kernels (the library picks one per pair; B200IMG_CONVERT_KERNEL forces it)."""
+    """Every layout pair through both general conversion kernels (B200IMG_CONVERT_KERNEL forces one) and through the library's own choice."""
     import torch
-    monkeypatch.setenv("B200IMG_CONVERT_KERNEL", kernel)
+    if kernel == "auto":   # the library's own choice, which includes the 16-pixel chunk kernel for Rgb8 sources
+        monkeypatch.delenv("B200IMG_CONVERT_KERNEL", raising=False)
+    else:
+        monkeypatch.setenv("B200IMG_CONVERT_KERNEL", kernel)
     npx = 5000 + 37  # several tiles plus a ragged tail
     for sc, dc in itertools.product([1, 2, 3, 4], [1, 2, 3, 4]):
         src = _special(sd, npx * sc).reshape(npx, sc)
