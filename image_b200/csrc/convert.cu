@@ -350,6 +350,51 @@ convert_rgb8_chunks_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ ds
     }
 }
 
+// Sub-word source pixels (3 or 6 bytes) with wide destination pixels (Rgb8 -> Rgba32F, Rgb16 -> Rgba16 ...): the source bytes of
+// a warp's 128 pixels go through a warp-private, double-buffered slice of shared memory (coalesced 4-byte cp.async, no CTA
+// barrier anywhere), every lane picks its pixels L, L + 32, L + 64, L + 96 out of it, converts, and stores them straight from
+// registers: contiguous runs per warp, no staging of the (much larger) destination.
+template <typename S, typename D, int CIN, int COUT, int MODE>
+__global__ void __launch_bounds__(256)
+convert_staged_in_kernel(const S *__restrict__ src, D *__restrict__ dst, size_t ngroups, Coefs k) {   // a group = 128 pixels
+    constexpr int BI = sizeof(S) * CIN, GROUP_BYTES = 128 * BI, GROUP_WORDS = GROUP_BYTES / 4;   // 96 or 192 words
+    __shared__ __align__(16) uint32_t s_buf[8][2][GROUP_WORDS];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const size_t warps = (size_t)gridDim.x * 8;
+    size_t g = (size_t)blockIdx.x * 8 + wib;
+    auto fetch = [&](size_t grp, int st) {
+        const uint32_t *gw = reinterpret_cast<const uint32_t *>(reinterpret_cast<const unsigned char *>(src) + grp * GROUP_BYTES);
+        const uint32_t d = (uint32_t)__cvta_generic_to_shared(&s_buf[wib][st][0]);
+#pragma unroll
+        for (int j = 0; j < GROUP_WORDS / 32; ++j)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(d + 4u * (lane + 32 * j)), "l"(gw + lane + 32 * j) : "memory");
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (g < ngroups) fetch(g, 0);
+    for (int it = 0; g < ngroups; g += warps, ++it) {
+        const int st = it & 1;
+        if (g + warps < ngroups) {
+            fetch(g + warps, st ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+        const S *sp = reinterpret_cast<const S *>(&s_buf[wib][st][0]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int q = lane + 32 * j;
+            S sv[CIN];
+#pragma unroll
+            for (int c = 0; c < CIN; ++c) sv[c] = sp[q * CIN + c];
+            D dv[COUT];
+            convert_px<S, D, CIN, COUT, MODE>(sv, dv, k);
+            sts_px<D, COUT>(dst + (g * 128 + q) * COUT, dv);
+        }
+        __syncwarp();   // the slice is free for the fetch after next
+    }
+}
+
 template <typename S, typename D, int CIN, int COUT, int MODE>
 int launch_direct(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStream_t stream) {
     DeviceCtx *ctx = current_ctx();
@@ -388,6 +433,22 @@ int launch(const void *src, void *dst, size_t npixels, const Coefs &k, cudaStrea
                 src = reinterpret_cast<const unsigned char *>(src) + chunks * 48;
                 dst = reinterpret_cast<unsigned char *>(dst) + chunks * 16 * BO;
                 npixels -= chunks * 16;
+            }
+        }
+        if constexpr ((BI == 3 || BI == 6) && BO >= 4 && MODE != MODE_SWIZZLE) {
+            constexpr size_t AOs = VO ? BO : sizeof(D);
+            const bool want = force ? force[0] == 's' : true;
+            if (want && npixels >= 4096 && (reinterpret_cast<uintptr_t>(src) & 3) == 0 && reinterpret_cast<uintptr_t>(dst) % AOs == 0) {
+                DeviceCtx *ctx = current_ctx();
+                if (!ctx) return B200IMG_ERR_CUDA;
+                const size_t groups = npixels / 128;
+                const unsigned grid = (unsigned)std::min<size_t>((groups + 7) / 8, (size_t)ctx->sm_count * 8);
+                convert_staged_in_kernel<S, D, CIN, COUT, MODE><<<grid, 256, 0, stream>>>((const S *)src, (D *)dst, groups, k);
+                B200_CUDA(cudaGetLastError());
+                if (groups * 128 == npixels) return B200IMG_OK;
+                src = reinterpret_cast<const unsigned char *>(src) + groups * 128 * BI;
+                dst = reinterpret_cast<unsigned char *>(dst) + groups * 128 * BO;
+                npixels -= groups * 128;
             }
         }
         bool direct = VI || sizeof(S) == 4 || BO < 4;
