@@ -42,6 +42,26 @@ template <> struct Word<float> {
 template <typename T> __device__ __forceinline__ float unbias(float m) { return m - 8388608.0f; }
 template <> __device__ __forceinline__ float unbias<float>(float m) { return m; }
 
+// (v + 0.5) as u8 of four values (NearestFrom<f32> for u8, src/primitive_sealed.rs:110-120) packed into one word, on the FMA
+// pipe only: clamp, then an addition to 2^23 that rounds toward zero leaves floor(v + 0.5) in the low mantissa byte.
+__device__ __forceinline__ uint32_t pack_u8x4(float r, float g, float b, float al) {
+    auto q = [](float v) -> uint32_t {
+        const float t = fminf(fmaxf(__fadd_rn(v, 0.5f), 0.0f), 255.5f);
+        return __float_as_uint(__fadd_rz(t, 8388608.0f));
+    };
+    const uint32_t rg = __byte_perm(q(r), q(g), 0x0040), ba = __byte_perm(q(b), q(al), 0x0040);
+    return __byte_perm(rg, ba, 0x5410);
+}
+
+// ... and (v + 0.5) as u16 of two values packed into one word, the same way (low 16 mantissa bits)
+__device__ __forceinline__ uint32_t pack_u16x2(float a, float b) {
+    auto q = [](float v) -> uint32_t {
+        const float t = fminf(fmaxf(__fadd_rn(v, 0.5f), 0.0f), 65535.5f);
+        return __float_as_uint(__fadd_rz(t, 8388608.0f));
+    };
+    return __byte_perm(q(a), q(b), 0x5410);
+}
+
 __device__ __forceinline__ void cp_async(void *smem_dst, const void *gsrc, int bytes) {
     const uint32_t d = smem_u32(smem_dst);
     if (bytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");

@@ -70,17 +70,6 @@ __device__ __noinline__ float border_scale(const f32x2 *w, int first, int len) {
     return 1.0f / s;
 }
 
-// (v + 0.5) as u8 of four values (NearestFrom<f32> for u8, src/primitive_sealed.rs:110-120) packed into one word, on the FMA
-// pipe only: clamp, then an addition to 2^23 that rounds toward zero leaves floor(v + 0.5) in the low mantissa byte.
-__device__ __forceinline__ uint32_t pack_u8x4(float r, float g, float b, float al) {
-    auto q = [](float v) -> uint32_t {
-        const float t = fminf(fmaxf(__fadd_rn(v, 0.5f), 0.0f), 255.5f);
-        return __float_as_uint(__fadd_rz(t, 8388608.0f));
-    };
-    const uint32_t rg = __byte_perm(q(r), q(g), 0x0040), ba = __byte_perm(q(b), q(al), 0x0040);
-    return __byte_perm(rg, ba, 0x5410);
-}
-
 template <int C, int R, int A>
 __global__ void __launch_bounds__(RI_THREADS)
 resize_int_kernel(const __grid_constant__ IntArgs a) {

@@ -58,7 +58,45 @@ __device__ __noinline__ float up2_border_scale(const f32x2 *w, int T, int first,
     return 1.0f / s;
 }
 
-template <int T>
+// One source pixel (four channels of E) as two packed pairs of floats (r, g) (b, a); integers by the 2^23 mantissa trick.
+template <typename E> __device__ __forceinline__ ulonglong2 up2_load_px(const unsigned char *p) {
+    if constexpr (sizeof(E) == 4) {
+        return __ldg(reinterpret_cast<const ulonglong2 *>(p));
+    } else if constexpr (sizeof(E) == 1) {
+        float f[4];
+        Word<uint8_t>::biased(__ldg(reinterpret_cast<const uint32_t *>(p)), f);
+        const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+        return make_ulonglong2(add2(pack2(f[0], f[1]), bias2), add2(pack2(f[2], f[3]), bias2));
+    } else {
+        const uint2 w = __ldg(reinterpret_cast<const uint2 *>(p));
+        float f[2], g[2];
+        Word<uint16_t>::biased(w.x, f);
+        Word<uint16_t>::biased(w.y, g);
+        const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+        return make_ulonglong2(add2(pack2(f[0], f[1]), bias2), add2(pack2(g[0], g[1]), bias2));
+    }
+}
+
+// Two neighbouring destination pixels (phase 0 and 1 of one source position) of E from their sums: clamp_nearest_from
+// (src/primitive_sealed.rs:107-147) and one store of 2 x 4 x sizeof(E) bytes (f32: two 128-bit stores).
+template <typename E> __device__ __forceinline__ void up2_store_pair(unsigned char *p, const f32x2 (&a)[2][2]) {
+    float v[2][4];
+#pragma unroll
+    for (int ph = 0; ph < 2; ++ph) { unpack2(a[ph][0], v[ph][0], v[ph][1]); unpack2(a[ph][1], v[ph][2], v[ph][3]); }
+    if constexpr (sizeof(E) == 4) {
+#pragma unroll
+        for (int ph = 0; ph < 2; ++ph)
+            reinterpret_cast<float4 *>(p)[ph] = make_float4(Px<float>::clamp_nearest(v[ph][0]), Px<float>::clamp_nearest(v[ph][1]),
+                                                            Px<float>::clamp_nearest(v[ph][2]), Px<float>::clamp_nearest(v[ph][3]));
+    } else if constexpr (sizeof(E) == 1) {
+        *reinterpret_cast<uint2 *>(p) = make_uint2(pack_u8x4(v[0][0], v[0][1], v[0][2], v[0][3]), pack_u8x4(v[1][0], v[1][1], v[1][2], v[1][3]));
+    } else {
+        *reinterpret_cast<uint4 *>(p) = make_uint4(pack_u16x2(v[0][0], v[0][1]), pack_u16x2(v[0][2], v[0][3]), pack_u16x2(v[1][0], v[1][1]),
+                                                   pack_u16x2(v[1][2], v[1][3]));
+    }
+}
+
+template <int T, typename E>
 __global__ void __launch_bounds__(U2_THREADS, 3)
 resize_up2_kernel(const __grid_constant__ Up2Args a) {
     constexpr int S = (T - 1) / 2;   // support
@@ -79,8 +117,9 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
     const int nm = min(a.BANDS, m_end - mA);           // destination pairs of this band
     if (nm <= 0) return;
 
-    const float *src = reinterpret_cast<const float *>(reinterpret_cast<const unsigned char *>(a.src) + (size_t)img * a.src_img_stride);
-    float *dst = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(a.dst) + (size_t)img * a.dst_img_stride);
+    constexpr size_t PXB = 4 * sizeof(E);                // bytes per pixel
+    const unsigned char *src = reinterpret_cast<const unsigned char *>(a.src) + (size_t)img * a.src_img_stride;
+    unsigned char *dst = reinterpret_cast<unsigned char *>(a.dst) + (size_t)img * a.dst_img_stride;
     const int p0 = x0 - S;                             // source pixel of ring column 0
     const int px = p0 + tid;                           // this thread's source pixel
     const bool active = tid < tws + 2 * S && px >= 0 && px < (int)a.w;
@@ -90,13 +129,13 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
     // only fill the window (their pairs lie in front of the band and are never read) ----
     const int j0 = mA + S - T;
     const int steps = T * (1 + (nm + T - 1) / T);
-    const size_t gp = (size_t)a.w * 4;                 // floats per source row
-    const float *gptr = src + (size_t)4 * (active ? px : max(min(px, (int)a.w - 1), 0)) + ((ptrdiff_t)j0 - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
+    const size_t gp = (size_t)a.w * PXB;               // bytes per source row
+    const unsigned char *gptr = src + PXB * (size_t)(active ? px : max(min(px, (int)a.w - 1), 0)) + ((ptrdiff_t)j0 - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
     int jnext = j0;
     auto load_next = [&]() -> ulonglong2 {
         ulonglong2 v = make_ulonglong2(0ull, 0ull);
         // (only rows that a pair of this band taps: a band's buffer holds nothing else, and the stream starts one row earlier)
-        if (jnext >= max(mA - S, 0) && jnext < min((int)a.h, mA + nm + S)) v = __ldg(reinterpret_cast<const ulonglong2 *>(gptr));
+        if (jnext >= max(mA - S, 0) && jnext < min((int)a.h, mA + nm + S)) v = up2_load_px<E>(gptr);
         gptr += gp;
         ++jnext;
         return v;
@@ -170,20 +209,10 @@ resize_up2_kernel(const __grid_constant__ Up2Args a) {
                 }
             }
             if (x < tws) {
-                float4 *gout = reinterpret_cast<float4 *>(dst + ((size_t)(2 * rp - row_lo) * a.nw + 2 * (size_t)(x0 + x)) * 4);
+                unsigned char *gout = dst + ((size_t)(2 * rp - row_lo) * a.nw + 2 * (size_t)(x0 + x)) * PXB;
 #pragma unroll
-                for (int rr = 0; rr < 2; ++rr) {
-                    if (2 * rp + rr >= row_lo && 2 * rp + rr < row_hi) {
-#pragma unroll
-                        for (int ph = 0; ph < 2; ++ph) {
-                            float r, g, b, al;
-                            unpack2(acc[rr][ph][0], r, g);
-                            unpack2(acc[rr][ph][1], b, al);
-                            gout[(size_t)rr * (a.nw) + ph] = make_float4(Px<float>::clamp_nearest(r), Px<float>::clamp_nearest(g),
-                                                                         Px<float>::clamp_nearest(b), Px<float>::clamp_nearest(al));
-                        }
-                    }
-                }
+                for (int rr = 0; rr < 2; ++rr)
+                    if (2 * rp + rr >= row_lo && 2 * rp + rr < row_hi) up2_store_pair<E>(gout + (size_t)rr * a.nw * PXB, acc[rr]);
             }
             seg += nwarps;
             while (seg >= segs) { seg -= segs; ++rp; }
@@ -240,7 +269,7 @@ int up2_env_int(const char *name, int dflt) {
 int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, uint32_t h, int C, int dtype, void *dst,
                    size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
                    const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st) {
-    if (dtype != B200IMG_F32 || C != 4) return 0;
+    if (C != 4) return 0;
     if (nw != 2 * w || nh != 2 * h || w < 16 || h < 16) return 0;
     const int T = vt.max_count;
     if (T != ht.max_count || (T != 3 && T != 5 && T != 7)) return 0;
@@ -297,12 +326,14 @@ int resize_up2_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     const size_t smem = ((size_t)2 * HR * a.pitch + 1) * 16 + (size_t)(2 * BANDS + 2 * HR) * 4;
     if (smem > ctx->smem_optin) return 0;
     const dim3 grid((unsigned)strips, (unsigned)bands, n_images);
-#define U2_GO(TT)                                                                                                   \
-    {                                                                                                               \
-        B200_CUDA(cudaFuncSetAttribute(resize_up2_kernel<TT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        resize_up2_kernel<TT><<<grid, U2_THREADS, smem, st>>>(a);                                                   \
+#define U2_GO(TT, EE)                                                                                                   \
+    {                                                                                                                   \
+        B200_CUDA(cudaFuncSetAttribute(resize_up2_kernel<TT, EE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        resize_up2_kernel<TT, EE><<<grid, U2_THREADS, smem, st>>>(a);                                                   \
     }
-    if (T == 7) U2_GO(7) else if (T == 5) U2_GO(5) else U2_GO(3)
+#define U2_GO_T(EE) { if (T == 7) U2_GO(7, EE) else if (T == 5) U2_GO(5, EE) else U2_GO(3, EE) }
+    if (dtype == B200IMG_F32) U2_GO_T(float) else if (dtype == B200IMG_U8) U2_GO_T(uint8_t) else U2_GO_T(uint16_t)
+#undef U2_GO_T
 #undef U2_GO
     B200_CUDA(cudaGetLastError());
     return 1;

@@ -359,3 +359,47 @@ def test_resize_fixed_window_fuzz(cuda, monkeypatch):
         want = o.resize(imgs[i], 500, 320, int(FilterType.Lanczos3), acc_init=0.0)
         assert np.array_equal(got[i] == 0, want == 0)          # NaN -> 0 in the f32 clamp (primitive_sealed.rs:127-137)
         assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16])
+@pytest.mark.parametrize("f", [FilterType.Triangle, FilterType.CatmullRom, FilterType.Lanczos3, FilterType.Gaussian])
+def test_resize_up2_rgba_integer_types(cuda, f, dtype, monkeypatch):
+    """The 2x upscale kernel on Rgba8 / Rgba16 (same passes, integer load and store): +-1 LSB of the oracle, ragged strips and
+    bands, a batch, odd-seamed row bands, saturated and black images."""
+    import ctypes
+    import torch
+    monkeypatch.setenv("B200IMG_U2_FORCE", "1")
+    rng = np.random.default_rng(31 + int(f))
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    dt = L.U8 if dtype == np.uint8 else L.U16
+    top = np.iinfo(dtype).max
+    for (h, w) in [(300, 516), (1031, 252), (64, 2048)]:
+        img = rand_image(rng, h, w, 4, dtype)
+        for acc in (1.0, 0.0):
+            want = o.resize(img, 2 * w, 2 * h, int(f), acc_init=acc).astype(np.int64)
+            got = imageops.resize(torch.from_numpy(img).to(cuda), 2 * w, 2 * h, f, acc_init=acc, flags=L.FP_FAST).cpu().numpy().astype(np.int64)
+            assert np.abs(got - want).max() <= 1, (f.name, img.shape, acc)
+    for v in (0, top):
+        img = np.full((200, 320, 4), v, dtype)
+        got = imageops.resize(torch.from_numpy(img).to(cuda), 640, 400, f, acc_init=0.0, flags=L.FP_FAST).cpu().numpy().astype(np.int64)
+        assert np.abs(got - o.resize(img, 640, 400, int(f), acc_init=0.0).astype(np.int64)).max() <= 1
+    imgs = np.stack([rand_image(rng, 200, 320, 4, dtype) for _ in range(6)])
+    src = torch.from_numpy(imgs).to(cuda)
+    dst = torch.empty((6, 400, 640, 4), dtype=src.dtype, device=cuda)
+    L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, 320, 200, 4, dt, dst.data_ptr(), 0, 640, 400, 6, int(f), 1.0, L.FP_FAST, st))
+    got = dst.cpu().numpy().astype(np.int64)
+    for i in (0, 5):
+        assert np.abs(got[i] - o.resize(imgs[i], 640, 400, int(f)).astype(np.int64)).max() <= 1
+    img = rand_image(rng, 900, 400, 4, dtype)
+    want = o.resize(img, 800, 1800, int(f)).astype(np.int64)
+    out = np.zeros((1800, 800, 4), dtype)
+    for r0, rows in [(0, 601), (601, 598), (1199, 601)]:
+        s0, sn = ctypes.c_uint32(), ctypes.c_uint32()
+        L.check(lib.b200img_resize_band_src_rows(900, 1800, int(f), r0, rows, ctypes.byref(s0), ctypes.byref(sn)))
+        band = torch.from_numpy(img[s0.value:s0.value + sn.value].copy()).to(cuda)
+        d = torch.empty((rows, 800, 4), dtype=band.dtype, device=cuda)
+        L.check(lib.b200img_resize_band_dev(band.data_ptr(), s0.value, sn.value, 400, 900, 4, dt, d.data_ptr(), r0, rows,
+                                            800, 1800, int(f), 1.0, L.FP_FAST, st))
+        out[r0:r0 + rows] = d.cpu().numpy()
+    assert np.abs(out.astype(np.int64) - want).max() <= 1
