@@ -1,5 +1,5 @@
-// resample_int.cu -- the resampler for downscales by an EVEN INTEGER ratio (2x, 4x, ...) of u8 images
-// under B200IMG_FP_FAST: thumbnails and mip levels, BASELINE configs 0 (1080p -> 540p, Lanczos3) and 3
+// resample_int.cu -- the resampler for downscales by an EVEN INTEGER ratio (2x, 4x) of u8 images (and of
+// four-channel 16-bit / f32 images) under B200IMG_FP_FAST: thumbnails and mip levels, BASELINE configs 0 (1080p -> 540p, Lanczos3) and 3
 // (1024^2 -> 256^2, CatmullRom).
 //
 // For such a ratio R every output sample away from the borders has the SAME window shape: its window
@@ -49,6 +49,7 @@ struct IntArgs {
     int tmp_pitch;      // floats per ring row (1 mod 32: lane = row reads hit 32 banks)
     int out_pitch;      // bytes per staged output row (4 * odd)
     float acc_init;
+    int esize;          // four-channel kernel: bytes per channel (1, 2, 4)
     int vec_out;        // four-channel kernel: destination rows are 16-byte aligned (128-bit stores)
     f32x2 wv[RI_MAX_TAPS], wh[RI_MAX_TAPS];  // (w, w) pairs
 };
@@ -257,13 +258,60 @@ resize_int_kernel(const __grid_constant__ IntArgs a) {
 // phase straight into the vertical pass of the next, which fills the other buffer, so a phase costs one CTA barrier.
 // Nothing in the row loop branches: border scales come from a small table in shared memory, threads beyond the strip's
 // last word store to a dump slot, rows that no output needs are stored and never read.
-template <int R, int A>
-__global__ void __maxnreg__(96)  // three CTAs of RI_THREADS_PX threads per SM
+// One source pixel (four channels of E) as loaded, and as two packed pairs of floats (r, g) (b, a).
+template <typename E> struct RawPx;
+template <> struct RawPx<uint8_t> {
+    typedef uint32_t type;
+    static __device__ __forceinline__ type zero() { return 0u; }
+    static __device__ __forceinline__ void pairs(type w, f32x2 &rg, f32x2 &ba) {
+        float f[4];
+        Word<uint8_t>::biased(w, f);
+        const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+        rg = add2(pack2(f[0], f[1]), bias2);
+        ba = add2(pack2(f[2], f[3]), bias2);
+    }
+};
+template <> struct RawPx<uint16_t> {
+    typedef uint2 type;
+    static __device__ __forceinline__ type zero() { return make_uint2(0u, 0u); }
+    static __device__ __forceinline__ void pairs(type w, f32x2 &rg, f32x2 &ba) {
+        float f[2], g[2];
+        Word<uint16_t>::biased(w.x, f);
+        Word<uint16_t>::biased(w.y, g);
+        const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
+        rg = add2(pack2(f[0], f[1]), bias2);
+        ba = add2(pack2(g[0], g[1]), bias2);
+    }
+};
+template <> struct RawPx<float> {
+    typedef ulonglong2 type;
+    static __device__ __forceinline__ type zero() { return make_ulonglong2(0ull, 0ull); }
+    static __device__ __forceinline__ void pairs(type w, f32x2 &rg, f32x2 &ba) { rg = w.x; ba = w.y; }
+};
+
+// A destination pixel of E from its four sums (clamp_nearest_from, src/primitive_sealed.rs:107-147), as 32-bit words
+template <typename E> __device__ __forceinline__ void out_words(float r, float g, float b, float al, uint32_t (&o)[sizeof(E)]) {
+    if constexpr (sizeof(E) == 1) {
+        o[0] = pack_u8x4(r, g, b, al);
+    } else if constexpr (sizeof(E) == 2) {
+        o[0] = pack_u16x2(r, g);
+        o[1] = pack_u16x2(b, al);
+    } else {
+        o[0] = __float_as_uint(Px<float>::clamp_nearest(r)); o[1] = __float_as_uint(Px<float>::clamp_nearest(g));
+        o[2] = __float_as_uint(Px<float>::clamp_nearest(b)); o[3] = __float_as_uint(Px<float>::clamp_nearest(al));
+    }
+}
+
+template <int R, int A, typename E>
+__global__ void __maxnreg__(sizeof(E) == 4 ? 128 : 96)  // u8 / u16: three CTAs of RI_THREADS_PX threads per SM
 resize_int4_kernel(const __grid_constant__ IntArgs a) {
     constexpr int NT = A * R, P = A * R;
     constexpr int HR = A == 6 ? 12 : 16;   // ring rows per buffer = output rows per horizontal phase; lane & 15 = row
     constexpr int PH = HR / A;
-    constexpr int D = P <= 16 ? P : P / 2;
+    constexpr int D = sizeof(E) == 4 ? P / 2 : (P <= 16 ? P : P / 2);   // source rows in flight per thread (f32 rows are four registers each)
+    constexpr int PXB = 4 * sizeof(E);      // bytes per pixel
+    constexpr int WPP = sizeof(E);          // 32-bit words per destination pixel
+    typedef typename RawPx<E>::type Raw;
     constexpr int BLK = R == 2 ? 8 : 4;     // output pixels per horizontal item: about two items per warp of thread columns
     constexpr int SPAN = R * (BLK - 1) + NT;
     static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
@@ -282,7 +330,7 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
 
     const uint8_t *src = reinterpret_cast<const uint8_t *>(a.src) + (size_t)img * a.src_img_stride;
     uint8_t *dst = reinterpret_cast<uint8_t *>(a.dst) + (size_t)img * a.dst_img_stride;
-    const size_t gp = (size_t)a.w * 4;
+    const size_t gp = (size_t)a.w * PXB;
     const int p0 = R * ox0 + a.L0h;              // source pixel of ring column 0 (may be negative)
     const int p1 = R * (ox0 + tw - 1) + a.L0h + NT;
     const int q0 = max(p0, 0), q1 = min(p1, (int)a.w);
@@ -292,16 +340,16 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
     const int jbase = R * oyA + a.L0v - R;
     const int ulo = max(R * oyA + a.L0v, 0) - jbase;
     const unsigned ulen = (unsigned)(min((int)a.h, R * (oyA + nout - 1) + a.L0v + NT) - jbase - ulo);
-    const uint8_t *gptr = src + 4 * (size_t)(q0 + (active ? tid : 0)) + ((ptrdiff_t)jbase - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
+    const uint8_t *gptr = src + PXB * (size_t)(q0 + (active ? tid : 0)) + ((ptrdiff_t)jbase - (ptrdiff_t)a.src_row0) * (ptrdiff_t)gp;
     int unext = 0;
-    auto load_next = [&]() -> uint32_t {
-        uint32_t v = 0u;
-        if ((unsigned)(unext - ulo) < ulen) v = __ldg(reinterpret_cast<const uint32_t *>(gptr));
+    auto load_next = [&]() -> Raw {
+        Raw v = RawPx<E>::zero();
+        if ((unsigned)(unext - ulo) < ulen) v = __ldg(reinterpret_cast<const Raw *>(gptr));
         gptr += gp;
         ++unext;
         return v;
     };
-    uint32_t buf[D];
+    Raw buf[D];
 #pragma unroll
     for (int k = 0; k < D; ++k) buf[k] = load_next();
 
@@ -334,7 +382,7 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
         __syncthreads();
         const int nb = (a.TW + BLK - 1) / BLK;
         const ulonglong2 *trow = reinterpret_cast<const ulonglong2 *>(s_ring + ((size_t)(phase & 1) * HR + rl) * a.tmp_pitch);
-        uint8_t *grow = dst + (size_t)(oyA + n0 + rl - (int)a.dst_row0) * ((size_t)a.nw * 4) + (size_t)ox0 * 4;
+        uint8_t *grow = dst + (size_t)(oyA + n0 + rl - (int)a.dst_row0) * ((size_t)a.nw * PXB) + (size_t)ox0 * PXB;
         for (int item = 2 * warp + (lane >> 4); item < nb; item += 2 * nwarps) {
             const int xa = item * BLK;
             const ulonglong2 *t = trow + R * xa;
@@ -365,23 +413,27 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
                     }
                 }
             }
-            uint32_t o[BLK];
+            uint32_t o[BLK][WPP];
 #pragma unroll
             for (int i = 0; i < BLK; ++i) {
                 float r, g, b, al;
                 unpack2(acc[i][0], r, g);
                 unpack2(acc[i][1], b, al);
-                o[i] = pack_u8x4(r, g, b, al);
+                out_words<E>(r, g, b, al, o[i]);
             }
             if (rlane < rows_g) {
-                uint32_t *gout = reinterpret_cast<uint32_t *>(grow) + xa;
+                uint32_t *gout = reinterpret_cast<uint32_t *>(grow) + xa * WPP;
                 if (vec_out && xa + BLK <= tw) {
+                    const uint32_t *ow = &o[0][0];
 #pragma unroll
-                    for (int i = 0; i < BLK; i += 4) reinterpret_cast<uint4 *>(gout + i)[0] = make_uint4(o[i], o[i + 1], o[i + 2], o[i + 3]);
+                    for (int i = 0; i < BLK * WPP; i += 4) reinterpret_cast<uint4 *>(gout + i)[0] = make_uint4(ow[i], ow[i + 1], ow[i + 2], ow[i + 3]);
                 } else {
 #pragma unroll
                     for (int i = 0; i < BLK; ++i)
-                        if (xa + i < tw) gout[i] = o[i];
+                        if (xa + i < tw) {
+#pragma unroll
+                            for (int k = 0; k < WPP; ++k) gout[i * WPP + k] = o[i][k];
+                        }
                 }
             }
         }
@@ -394,10 +446,9 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
         const float *vsp = s_vs + m * A;
 #pragma unroll
         for (int q = 0; q < P; ++q) {   // q is a compile-time constant after unrolling
-            float f[4];
-            Word<uint8_t>::biased(buf[q % D], f);
+            f32x2 f01, f23;
+            RawPx<E>::pairs(buf[q % D], f01, f23);
             buf[q % D] = load_next();
-            const f32x2 f01 = add2(pack2(f[0], f[1]), bias2), f23 = add2(pack2(f[2], f[3]), bias2);
             const int fq = q / R, qr = q % R;
 #pragma unroll
             for (int aa = 0; aa < A; ++aa) {
@@ -481,9 +532,14 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
 template <int C, int R, int A>
 int launch_ra(const IntArgs &a, dim3 grid, int threads, size_t smem, cudaStream_t st) {
     if constexpr (C == 4) {
-        auto k4 = resize_int4_kernel<R, A>;
-        B200_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k4<<<grid, threads, smem, st>>>(a);
+#define RI_GO4(EE)                                                                              \
+    {                                                                                           \
+        auto k4 = resize_int4_kernel<R, A, EE>;                                                 \
+        B200_CUDA(cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        k4<<<grid, threads, smem, st>>>(a);                                                     \
+    }
+        if (a.esize == 1) RI_GO4(uint8_t) else if (a.esize == 2) RI_GO4(uint16_t) else RI_GO4(float)
+#undef RI_GO4
         B200_CUDA(cudaGetLastError());
         return B200IMG_OK;
     }
@@ -519,14 +575,19 @@ int env_int(const char *name, int dflt) {
 int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, uint32_t w, uint32_t h, int C, int dtype, void *dst,
                    size_t dst_img_stride, uint32_t dst_row0, uint32_t dst_rows, uint32_t nw, uint32_t nh, uint32_t n_images,
                    const AxisTable &vt, const AxisTable &ht, float acc_init, const DeviceCtx *ctx, cudaStream_t st) {
-    if (dtype != B200IMG_U8) return 0;
+    if (dtype != B200IMG_U8 && C != 4) return 0;   // 16-bit and f32 images: the four-channel kernel only
     if (nw == 0 || nh == 0 || w % nw != 0 || h % nh != 0 || w / nw != h / nh) return 0;
     const int R = (int)(w / nw);
     if (R != 2 && R != 4) return 0;
-    const size_t gp = (size_t)w * C;
+    const size_t esize = dtype_size(dtype), gp = (size_t)w * C * esize;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
-    if ((uint64_t)w * C > (1u << 30) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
-    if (C == 4 && ((reinterpret_cast<uintptr_t>(dst) & 3) != 0 || dst_img_stride % 4 != 0)) return 0;  // the four-channel kernel stores whole pixels
+    if ((uint64_t)w * C > (1u << 28) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
+    if (C == 4) {   // the four-channel kernel loads and stores whole pixels
+        const size_t pxb = 4 * esize;
+        if (reinterpret_cast<uintptr_t>(src) % pxb != 0 || src_img_stride % pxb != 0 || reinterpret_cast<uintptr_t>(dst) % pxb != 0 ||
+            dst_img_stride % pxb != 0)
+            return 0;
+    }
     // both axes follow the fixed-window rule with symmetric weights (checked when the tables were built)
     if (vt.fixed_R != R || ht.fixed_R != R) return 0;
     const int NT = vt.max_count;
@@ -574,7 +635,8 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     a.w = w; a.h = h; a.nw = nw; a.nh = nh; a.src_row0 = src_row0; a.dst_row0 = dst_row0; a.dst_rows = dst_rows;
     a.L0v = L0v; a.L0h = L0h; a.TW = best.TW; a.BAND = BAND; a.tmp_pitch = best.tmp_pitch; a.out_pitch = best.out_pitch;
     a.acc_init = acc_init;
-    a.vec_out = ((size_t)nw * C) % 16 == 0 && dst_img_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    a.esize = (int)esize;
+    a.vec_out = ((size_t)nw * C * esize) % 16 == 0 && dst_img_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
     for (int k = 0; k < RI_MAX_TAPS; ++k) {
         const float v = k < NT ? wvm[k] : 0.0f, hh = k < NT ? whm[k] : 0.0f;
         uint32_t vb, hb;

@@ -403,3 +403,43 @@ def test_resize_up2_rgba_integer_types(cuda, f, dtype, monkeypatch):
                                             800, 1800, int(f), 1.0, L.FP_FAST, st))
         out[r0:r0 + rows] = d.cpu().numpy()
     assert np.abs(out.astype(np.int64) - want).max() <= 1
+
+
+@pytest.mark.parametrize("dtype", [np.uint16, np.float32])
+@pytest.mark.parametrize("f", [FilterType.Triangle, FilterType.CatmullRom, FilterType.Gaussian, FilterType.Lanczos3])
+@pytest.mark.parametrize("r", [2, 4])
+def test_resize_integer_ratio_rgba16_rgba32f(cuda, f, r, dtype):
+    """The four-channel fixed-window downscale kernel with 16-bit and f32 pixels (same passes, other load and store): batches
+    (so that it is picked), ragged strips and bands, both accumulator start values; +-1 LSB resp. 1e-5 relative."""
+    import torch
+    rng = np.random.default_rng(700 + 10 * r + int(f))
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    dt = L.U16 if dtype == np.uint16 else L.F32
+    for (nw, nh, n) in [(372, 92, 12), (960, 540, 1), (50, 311, 40)]:
+        w, h = nw * r, nh * r
+        imgs = np.stack([rand_image(rng, h, w, 4, dtype) for _ in range(n)])
+        src = torch.from_numpy(imgs).to(cuda)
+        for acc in (1.0, 0.0):
+            dst = torch.empty((n, nh, nw, 4), dtype=src.dtype, device=cuda)
+            L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, dt, dst.data_ptr(), 0, nw, nh, n, int(f), acc, L.FP_FAST, st))
+            got = dst.cpu().numpy()
+            for i in (0, n - 1):
+                want = o.resize(imgs[i], nw, nh, int(f), acc_init=acc)
+                if dtype == np.float32:
+                    assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6), (f.name, r, nw, nh, acc)
+                else:
+                    assert np.abs(got[i].astype(np.int64) - want.astype(np.int64)).max() <= 1, (f.name, r, nw, nh, acc)
+    if dtype == np.float32:   # non-finite samples: every window holds exactly the reference's taps, the padding is finite zeros
+        imgs = rng.random((12, 92 * r, 372 * r, 4), dtype=np.float32) * 0.5 + 0.1
+        imgs[0, 40 * r, 100 * r] = np.inf
+        imgs[0, 2, 3, 1] = np.nan
+        imgs[11, 92 * r - 1, 372 * r - 1, 2] = np.nan
+        src = torch.from_numpy(imgs).to(cuda)
+        dst = torch.empty((12, 92, 372, 4), dtype=torch.float32, device=cuda)
+        L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, 372 * r, 92 * r, 4, L.F32, dst.data_ptr(), 0, 372, 92, 12, int(f), 0.0, L.FP_FAST, st))
+        got = dst.cpu().numpy()
+        for i in (0, 11):
+            want = o.resize(imgs[i], 372, 92, int(f), acc_init=0.0)
+            assert np.array_equal(got[i] == 0, want == 0)
+            assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6)
