@@ -1,5 +1,5 @@
-// resample_int.cu -- the resampler for downscales by an EVEN INTEGER ratio (2x, 4x) of u8 images (and of
-// four-channel 16-bit / f32 images) under B200IMG_FP_FAST: thumbnails and mip levels, BASELINE configs 0 (1080p -> 540p, Lanczos3) and 3
+// resample_int.cu -- the resampler for downscales by an INTEGER ratio (2x, 4x; four-channel images also 3x) of u8
+// images (and of four-channel 16-bit / f32 images) under B200IMG_FP_FAST: thumbnails and mip levels, BASELINE configs 0 (1080p -> 540p, Lanczos3) and 3
 // (1024^2 -> 256^2, CatmullRom).
 //
 // For such a ratio R every output sample away from the borders has the SAME window shape: its window
@@ -302,23 +302,35 @@ template <typename E> __device__ __forceinline__ void out_words(float r, float g
     }
 }
 
+// Geometry of the four-channel kernel, shared with the host's planning
+__host__ __device__ constexpr int ri_ring_rows(int S) { return S == 6 ? 12 : S == 7 ? 14 : S == 5 ? 15 : S == 3 ? 15 : 16; }
+__host__ __device__ constexpr int ri_item_px(int R) { return R == 2 ? 8 : R == 3 ? 5 : 4; }
+__host__ __device__ constexpr int ri_rows_in_flight(int P, int most) {
+    int d = 1;
+    for (int k = 1; k <= most; ++k)
+        if (P % k == 0) d = k;
+    return d;
+}
+
 template <int R, int A, typename E>
 __global__ void __maxnreg__(sizeof(E) == 4 ? 128 : 96)  // u8 / u16: three CTAs of RI_THREADS_PX threads per SM
 resize_int4_kernel(const __grid_constant__ IntArgs a) {
-    constexpr int NT = A * R, P = A * R;
-    constexpr int HR = A == 6 ? 12 : 16;   // ring rows per buffer = output rows per horizontal phase; lane & 15 = row
-    constexpr int PH = HR / A;
-    constexpr int D = sizeof(E) == 4 ? P / 2 : (P <= 16 ? P : P / 2);   // source rows in flight per thread (f32 rows are four registers each)
+    // An odd ratio puts the window's centre on a sample: NT = A R + 1 taps, and the row that closes output n (its tap NT - 1)
+    // is also the row that opens output n + A + 1 (tap 0): S = A + 1 outputs are open on those rows, A on the others.
+    constexpr int ODD = R & 1, NT = A * R + ODD, S = A + ODD, P = S * R;
+    constexpr int HR = ri_ring_rows(S);    // ring rows per buffer = output rows per horizontal phase (a multiple of S); lane & 15 = row
+    constexpr int PH = HR / S;
+    constexpr int D = ri_rows_in_flight(P, sizeof(E) == 4 ? 8 : 16);   // source rows in flight per thread (f32 rows are four registers each)
     constexpr int PXB = 4 * sizeof(E);      // bytes per pixel
     constexpr int WPP = sizeof(E);          // 32-bit words per destination pixel
     typedef typename RawPx<E>::type Raw;
-    constexpr int BLK = R == 2 ? 8 : 4;     // output pixels per horizontal item: about two items per warp of thread columns
+    constexpr int BLK = ri_item_px(R);      // output pixels per horizontal item: about two items per warp of thread columns
     constexpr int SPAN = R * (BLK - 1) + NT;
-    static_assert(P % D == 0 && HR % A == 0, "period and phase geometry");
+    static_assert(P % D == 0 && HR % S == 0 && HR <= 16, "period and phase geometry");
     extern __shared__ __align__(16) unsigned char smem[];
     float *s_ring = reinterpret_cast<float *>(smem);                 // [2][HR][tmp_pitch]
     float *s_dump = s_ring + (size_t)2 * HR * a.tmp_pitch;           // 4 floats
-    float *s_vs = s_dump + 4;                                        // [BAND + 2 A]: vertical border scale of output n at [n + A]
+    float *s_vs = s_dump + 4;                                        // [BAND + 2 S]: vertical border scale of output n at [n + S]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
     const unsigned img = blockIdx.z;
@@ -356,17 +368,17 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
     // while the first rows are on their way: a ring of zeros (the columns of samples outside the image are never written and
     // must contribute nothing) and the border scales of this band's rows
     for (int i = tid; i < 2 * HR * a.tmp_pitch + 4; i += nthreads) s_ring[i] = 0.0f;
-    for (int i = tid; i < a.BAND + 2 * A; i += nthreads) {
-        const int n = i - A, first = R * (oyA + n) + a.L0v;
+    for (int i = tid; i < a.BAND + 2 * S; i += nthreads) {
+        const int n = i - S, first = R * (oyA + n) + a.L0v;
         float vs = 1.0f;
         if (n >= 0 && n < nout && (first < 0 || first + NT > (int)a.h)) vs = border_scale<NT>(a.wv, first, (int)a.h);
         s_vs[i] = vs;
     }
     __syncthreads();
 
-    f32x2 lo[A], hi[A];
+    f32x2 lo[S], hi[S];
 #pragma unroll
-    for (int s = 0; s < A; ++s) { lo[s] = 0ull; hi[s] = 0ull; }
+    for (int s = 0; s < S; ++s) { lo[s] = 0ull; hi[s] = 0ull; }
     const f32x2 bias2 = pack2(-8388608.0f, -8388608.0f);
     const f32x2 init2 = pack2(a.acc_init, a.acc_init);
     const int pitch_eff = active ? a.tmp_pitch : 0;
@@ -423,7 +435,7 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
             }
             if (rlane < rows_g) {
                 uint32_t *gout = reinterpret_cast<uint32_t *>(grow) + xa * WPP;
-                if (vec_out && xa + BLK <= tw) {
+                if ((BLK * PXB) % 16 == 0 && vec_out && xa + BLK <= tw) {
                     const uint32_t *ow = &o[0][0];
 #pragma unroll
                     for (int i = 0; i < BLK * WPP; i += 4) reinterpret_cast<uint4 *>(gout + i)[0] = make_uint4(ow[i], ow[i + 1], ow[i + 2], ow[i + 3]);
@@ -441,9 +453,9 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
         tflush = (phase & 1) ? tb1 : tb0;
     };
 
-    const int periods = (nout + A - 1) / A + 1;
+    const int periods = (nout + S - 1) / S + 1;
     for (int m = 0; m < periods; ++m) {
-        const float *vsp = s_vs + m * A;
+        const float *vsp = s_vs + m * S;
 #pragma unroll
         for (int q = 0; q < P; ++q) {   // q is a compile-time constant after unrolling
             f32x2 f01, f23;
@@ -451,13 +463,15 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
             buf[q % D] = load_next();
             const int fq = q / R, qr = q % R;
 #pragma unroll
-            for (int aa = 0; aa < A; ++aa) {
-                const int slot = ((fq - aa) % A + A) % A, tap = qr + R * aa;
-                lo[slot] = fma2(f01, RI_SYM(a.wv, tap), lo[slot]);
-                hi[slot] = fma2(f23, RI_SYM(a.wv, tap), hi[slot]);
+            for (int aa = 0; aa < S; ++aa) {
+                const int slot = ((fq - aa) % S + S) % S, tap = qr + R * aa;
+                if (tap < NT) {
+                    lo[slot] = fma2(f01, RI_SYM(a.wv, tap), lo[slot]);
+                    hi[slot] = fma2(f23, RI_SYM(a.wv, tap), hi[slot]);
+                }
             }
-            if (qr == R - 1) {   // output row n = (m - 1) A + fq is complete, in accumulator (fq + 1) mod A
-                const int fs = (fq + 1) % A;
+            if (qr == (NT - 1) % R) {   // output row n = (m - 1) S + fq has had its last tap (from row group fq - (NT - 1) / R)
+                const int fs = ((fq - (NT - 1) / R) % S + S) % S;
                 const float vs = vsp[fq];
                 const f32x2 vs2 = pack2(vs, vs);
                 *reinterpret_cast<ulonglong2 *>(tflush) = make_ulonglong2(fma2(lo[fs], vs2, init2), fma2(hi[fs], vs2, init2));
@@ -469,8 +483,8 @@ resize_int4_kernel(const __grid_constant__ IntArgs a) {
         if (m == 0) {
             tflush = tb0;  // period 0 completed only the virtual outputs in front of the band
         } else {
-            // periods 1 .. m have completed outputs 0 .. m A - 1: a horizontal phase every PH periods and at the band's end
-            const int done = min(m * A, nout);
+            // periods 1 .. m have completed outputs 0 .. m S - 1: a horizontal phase every PH periods and at the band's end
+            const int done = min(m * S, nout);
             if ((m % PH) == 0 || done == nout) {
                 const int n0 = (done - 1) / HR * HR;
                 horizontal(n0, done - n0);
@@ -504,7 +518,7 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
     g.threads = round_up_i(words, 32);
     int tp;
     if (C == 4) {  // float4 pixels: an odd number of pixels per row, so that the 128-bit loads of 8 rows hit 8 bank groups
-        const int blk = R == 2 ? 8 : 4;
+        const int blk = ri_item_px(R);
         const int px = R * (round_up_i(TW, blk) - 1) + NT;  // the last item reads its whole span
         tp = 4 * (px | 1);
     } else {
@@ -515,12 +529,12 @@ IntGeo int_geo(int TW, uint32_t w, uint32_t nw, int C, int R, int NT, int L0h, i
     int op = round_up_i(TW * C, 4);
     if ((op / 4) % 2 == 0) op += 4;
     g.out_pitch = op;
-    if (C == 4) g.smem = (size_t)2 * HR * tp * 4 + 16 + (size_t)(RI_MAX_BAND + 2 * 6) * 4;  // two ring buffers, dump slot, border scales
+    if (C == 4) g.smem = (size_t)2 * HR * tp * 4 + 16 + (size_t)(RI_MAX_BAND + 2 * 7) * 4;  // two ring buffers, dump slot, border scales
     else g.smem = (size_t)HR * tp * 4 + (size_t)HR * op;
     // every warp of the CTA walks HR * R source rows per phase, then the CTA's horizontal items go round its warps
     const int nwarps = g.threads / 32;
     if (C == 4) {
-        const int blk = R == 2 ? 8 : 4, nb = (TW + blk - 1) / blk, rounds = (nb + 2 * nwarps - 1) / (2 * nwarps);
+        const int blk = ri_item_px(R), nb = (TW + blk - 1) / blk, rounds = (nb + 2 * nwarps - 1) / (2 * nwarps);
         const int A = NT / R, item = (R * (blk - 1) + NT) + 2 * blk * NT + 22 * blk + 40;
         g.cost = (double)g.strips * nwarps * (HR * R * (10 + 2 * A + 12.0 / R) + rounds * item) / HR;
     } else {
@@ -561,6 +575,9 @@ int launch_r(const IntArgs &a, int A, dim3 grid, int threads, size_t smem, cudaS
 
 template <int C>
 int launch_c(const IntArgs &a, int R, int A, dim3 grid, int threads, size_t smem, cudaStream_t st) {
+    if constexpr (C == 4) {
+        if (R == 3) return launch_r<4, 3>(a, A, grid, threads, smem, st);
+    }
     return R == 2 ? launch_r<C, 2>(a, A, grid, threads, smem, st) : launch_r<C, 4>(a, A, grid, threads, smem, st);
 }
 
@@ -578,7 +595,7 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     if (dtype != B200IMG_U8 && C != 4) return 0;   // 16-bit and f32 images: the four-channel kernel only
     if (nw == 0 || nh == 0 || w % nw != 0 || h % nh != 0 || w / nw != h / nh) return 0;
     const int R = (int)(w / nw);
-    if (R != 2 && R != 4) return 0;
+    if (R != 2 && R != 4 && !(R == 3 && C == 4)) return 0;   // (3x: the four-channel kernel only)
     const size_t esize = dtype_size(dtype), gp = (size_t)w * C * esize;
     if (gp % 4 != 0 || (reinterpret_cast<uintptr_t>(src) & 3) != 0 || src_img_stride % 4 != 0) return 0;
     if ((uint64_t)w * C > (1u << 28) || h > (1u << 29)) return 0;  // int arithmetic in the kernel
@@ -591,13 +608,13 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     // both axes follow the fixed-window rule with symmetric weights (checked when the tables were built)
     if (vt.fixed_R != R || ht.fixed_R != R) return 0;
     const int NT = vt.max_count;
-    if (NT != ht.max_count || NT % R != 0 || NT > RI_MAX_TAPS) return 0;
-    const int A = NT / R;
+    if (NT != ht.max_count || NT % R != (R & 1) || NT > RI_MAX_TAPS) return 0;   // an odd ratio centres the window on a sample: one more tap
+    const int A = NT / R, S = A + (R & 1);   // open outputs per row (odd ratios: S on the rows that close one)
     if (A != 2 && A != 4 && A != 6) return 0;
     const int L0v = vt.fixed_L0, L0h = ht.fixed_L0;
     const float *wvm = &vt.w[(size_t)(nh / 2) * vt.stride], *whm = &ht.w[(size_t)(nw / 2) * ht.stride];
 
-    const int HR = C == 4 ? (A == 6 ? 12 : 16) : (A == 6 ? 30 : 32);
+    const int HR = C == 4 ? ri_ring_rows(S) : (A == 6 ? 30 : 32);
     const int max_threads = C == 4 ? RI_THREADS_PX : RI_THREADS;
     // strip width: the cheapest (fewest thread columns over the image's width; for four channels also whole rounds of
     // horizontal items) among the widths that leave room for two (three) CTAs per SM
@@ -605,7 +622,7 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     const int forced_tw = env_int("B200IMG_RI_TW", 0);
     for (int pass = 0; pass < 2 && best.TW == 0; ++pass) {
         const size_t cap = pass == 0 ? (C == 4 ? (size_t)(233472 - 3072) / 3 : (size_t)(233472 - 2048) / 2) : ctx->smem_optin;
-        const int step = C == 4 ? (R == 2 ? 8 : 4) : 16;  // whole horizontal items (and 16-byte aligned output blocks)
+        const int step = C == 4 ? ri_item_px(R) : 16;  // whole horizontal items (and, at even ratios, 16-byte aligned output blocks)
         for (int TW = step; TW <= 256; TW += step) {
             if (forced_tw && TW != forced_tw) continue;
             const IntGeo g = int_geo(TW, w, nw, C, R, NT, L0h, HR);

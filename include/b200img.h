@@ -84,8 +84,8 @@ typedef enum {
 /* Resampler only: use the tile kernel even where the column-streaming kernel (downscales of
  * u8 / u16 images) applies.  Same results; exists so that both kernels can be tested. */
 #define B200IMG_RESIZE_TILED 512
-/* Resampler only: do not use the fixed-window kernels -- downscales by an even integer ratio
- * (2x, 4x) and exact 2x upscales of four-channel images, where every window has the same
+/* Resampler only: do not use the fixed-window kernels -- downscales by an integer ratio
+ * (2x, 3x, 4x) and exact 2x upscales of four-channel images, where every window has the same
  * shape, the weights are one or two vectors and border windows are renormalised after the sum -- but
  * the table-driven kernels that serve every other size.  Both are within the FAST contract (+-1 LSB /
  * 1e-5 relative of the reference); they may differ from each other by rounding.  For tests. */

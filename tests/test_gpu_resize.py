@@ -443,3 +443,34 @@ def test_resize_integer_ratio_rgba16_rgba32f(cuda, f, r, dtype):
             want = o.resize(imgs[i], 372, 92, int(f), acc_init=0.0)
             assert np.array_equal(got[i] == 0, want == 0)
             assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [np.uint8, np.uint16, np.float32])
+@pytest.mark.parametrize("f", [FilterType.Triangle, FilterType.CatmullRom, FilterType.Gaussian, FilterType.Lanczos3])
+def test_resize_ratio3_four_channels(cuda, f, dtype):
+    """Downscale by 3 (an odd ratio centres every window on a sample: one tap more, one more open output on the rows that close
+    one) through the four-channel fixed-window kernel: batches, ragged strips and bands, both accumulator start values."""
+    import torch
+    rng = np.random.default_rng(900 + int(f))
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    dt = {np.uint8: L.U8, np.uint16: L.U16, np.float32: L.F32}[dtype]
+    for (nw, nh, n) in [(373, 91, 12), (640, 360, 1), (47, 311, 40), (1280, 720, 2)]:
+        w, h = nw * 3, nh * 3
+        imgs = np.stack([rand_image(rng, h, w, 4, dtype) for _ in range(n)])
+        src = torch.from_numpy(imgs).to(cuda)
+        for acc in (1.0, 0.0):
+            dst = torch.empty((n, nh, nw, 4), dtype=src.dtype, device=cuda)
+            L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, dt, dst.data_ptr(), 0, nw, nh, n, int(f), acc, L.FP_FAST, st))
+            general = torch.empty_like(dst)
+            L.check(lib.b200img_resize_batch_dev(src.data_ptr(), 0, w, h, 4, dt, general.data_ptr(), 0, nw, nh, n, int(f), acc,
+                                                 L.FP_FAST | L.RESIZE_GENERAL, st))
+            got, gen = dst.cpu().numpy(), general.cpu().numpy()
+            for i in (0, n - 1):
+                want = o.resize(imgs[i], nw, nh, int(f), acc_init=acc)
+                if dtype == np.float32:
+                    assert np.allclose(got[i], want, rtol=1e-5, atol=1e-6), (f.name, nw, nh, acc)
+                    assert np.allclose(gen[i], want, rtol=1e-5, atol=1e-6)
+                else:
+                    assert np.abs(got[i].astype(np.int64) - want.astype(np.int64)).max() <= 1, (f.name, nw, nh, acc)
+                    assert np.abs(gen[i].astype(np.int64) - want.astype(np.int64)).max() <= 1

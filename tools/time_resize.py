@@ -31,6 +31,7 @@ CASES = [("K1 lanczos3 64x1080p rgba8 -> 960x540", 64, 1920, 1080, 4, torch.uint
          ("K4 catmullrom 256x1024^2 rgba8 -> 256^2", 256, 1024, 1024, 4, torch.uint8, 256, 256, FilterType.CatmullRom),
          ("lanczos3 64x1080p rgb8 -> 960x540", 64, 1920, 1080, 3, torch.uint8, 960, 540, FilterType.Lanczos3),
          ("triangle 64x1080p rgba8 -> 640x360", 64, 1920, 1080, 4, torch.uint8, 640, 360, FilterType.Triangle),
+         ("lanczos3 16x4K rgba8 -> 1280x720", 16, 3840, 2160, 4, torch.uint8, 1280, 720, FilterType.Lanczos3),
          ("lanczos3 32x1080p rgba16 -> 960x540", 32, 1920, 1080, 4, torch.uint16, 960, 540, FilterType.Lanczos3),
          ("lanczos3 16x1080p rgba32f -> 960x540", 16, 1920, 1080, 4, torch.float32, 960, 540, FilterType.Lanczos3),
          ("gaussian 64x1080p luma8 -> 960x540", 64, 1920, 1080, 1, torch.uint8, 960, 540, FilterType.Gaussian),
