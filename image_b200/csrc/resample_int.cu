@@ -611,6 +611,10 @@ int resize_int_try(const void *src, size_t src_img_stride, uint32_t src_row0, ui
     if (NT != ht.max_count || NT % R != (R & 1) || NT > RI_MAX_TAPS) return 0;   // an odd ratio centres the window on a sample: one more tap
     const int A = NT / R, S = A + (R & 1);   // open outputs per row (odd ratios: S on the rows that close one)
     if (A != 2 && A != 4 && A != 6) return 0;
+    // The one- to three-channel kernel (a 30 / 32-row scalar ring per CTA) pays only where there is work to amortise it: not on
+    // two-tap-per-output filters, narrow rows or short images (measured against the streaming kernel, tools/check_choice.py:
+    // Triangle 2 x 4096^2 Rgb8 1.15x slower, 64 x 256^2 Luma8 1.2-1.7x, 8192 x 128 Rgb8 1.7x).
+    if (C != 4 && (A == 2 || (size_t)w * C < 1024 || dst_rows < 96)) return 0;
     const int L0v = vt.fixed_L0, L0h = ht.fixed_L0;
     const float *wvm = &vt.w[(size_t)(nh / 2) * vt.stride], *whm = &ht.w[(size_t)(nw / 2) * ht.stride];
 
