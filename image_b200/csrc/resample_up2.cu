@@ -1,7 +1,8 @@
-// resample_up2.cu -- the resampler for exact 2x upscales of four-channel f32 images under B200IMG_FP_FAST:
-// BASELINE config 4, the 32768^2 Rgba32F Lanczos3 upscale and its row bands.  Written out below for the
-// support-3 filters (Lanczos3, Gaussian: seven taps); CatmullRom (five) and Triangle (three) are the same
-// kernel with a shorter window.
+// resample_up2.cu -- the resampler for exact 2x upscales of four-channel images under B200IMG_FP_FAST:
+// BASELINE config 4, the 32768^2 Rgba32F Lanczos3 upscale and its row bands.  Written out below for f32
+// pixels and the support-3 filters (Lanczos3, Gaussian: seven taps); CatmullRom (five) and Triangle (three)
+// are the same kernel with a shorter window, Rgba8 / Rgba16 the same kernel with an integer load in front
+// (2^23 mantissa conversion) and the reference's rounding store behind it.
 //
 // At ratio 1/2 destination samples 2m and 2m+1 both tap the SAME seven source samples m-3 .. m+3
 // (vertical_sample / horizontal_sample, src/imageops/sample.rs:494-562, 217-340: centre m + 0.25 resp.
@@ -12,9 +13,10 @@
 //               circular register file indexed at compile time (no moves); each step is one 128-bit load
 //               issued seven rows ahead, 28 FFMA2 with weights in uniform registers, and two 128-bit stores
 //               of the destination-row pair into a ring in shared memory.
-//   horizontal: every seven steps (14 ring rows) the warps share out (row, 32 source positions) items:
-//               lane = source position, seven 128-bit loads of neighbouring ring pixels, 28 FFMA2 for the two
-//               destination pixels 2x and 2x+1, stored as 32 contiguous bytes per lane (1 KB per warp).
+//   horizontal: every seven steps (14 ring rows) the warps share out (pair of ring rows, 32 source positions)
+//               items: lane = source position, fourteen 128-bit loads of neighbouring ring pixels, 56 FFMA2 in
+//               eight independent chains for the destination pixels 2x and 2x+1 of both rows, stored as 32
+//               contiguous bytes per lane and row (1 KB per warp and row).
 // The ring is double buffered, so a phase costs one CTA barrier.  The job is bound by its stores (64 bytes
 // written per 16 read); the arithmetic is ~160 thread instructions per source pixel.
 // Borders: samples outside the image count as zero and the sum is multiplied by 1 / (weights inside), the
