@@ -446,7 +446,7 @@ def multi_extras(torch, lib, L, dev, local, rank, world, dist, cpu_group, hbm, F
     for name, fn, bytes_px in (
             ("rgba16_to_rgb8", lambda: L.check(lib.b200img_convert_dev(a16.data_ptr(), L.U16, 4, o8.data_ptr(), L.U8, 3, n_mine, L.CAST, None, stream)), 11),
             ("swizzle_bgra_inplace", lambda: L.check(lib.b200img_swizzle_02_dev(bgra.data_ptr(), L.U8, 4, n_mine * 4, stream)), 8)):
-        ms = max_over_ranks(time_device(fn, 3, 3, torch, (lambda: dist.barrier()) if dist else None))
+        ms = max_over_ranks(time_device(fn, 20, 5, torch, (lambda: dist.barrier()) if dist else None))
         k3[name] = {"ms": round(ms, 4), "MP/s": round(npx / 1e6 / (ms / 1e3), 1), "hbm_frac_per_gpu": round(npx * bytes_px / (ms / 1e3) / 1e9 / world / hbm, 4)}
     if check and rank == 0:
         sl = slice(n_mine - 4096, n_mine)
