@@ -8,6 +8,13 @@ pub const F32: c_int = 2;
 pub const FP_FAST: c_int = 0;
 pub const FP_STRICT: c_int = 1;
 pub const FP_FUSED_MAC: c_int = 2;
+/// Kernel-choice flags (tests and callers that want one rounding behaviour across shapes)
+pub const RESIZE_UNFUSED: c_int = 256;
+pub const RESIZE_TILED: c_int = 512;
+pub const THUMBNAIL_PER_PIXEL: c_int = 1024;
+pub const GAUSS_TWO_KERNELS: c_int = 2048;
+pub const GAUSS_FUSED: c_int = 4096;
+pub const RESIZE_GENERAL: c_int = 8192;
 pub const BLUR_GENERIC: c_int = 0;
 pub const BLUR_DYN: c_int = 1;
 pub const CAST: c_int = 0;
