@@ -34,6 +34,18 @@ elif name in ("gauss65", "gauss21", "gauss65q", "fast", "gauss65x8", "fastx8"):
         p = GaussianBlurParameters.new_from_radius(10.0) if name == "gauss21" else GaussianBlurParameters.new_from_sigma(10.0)
         path = L.BLUR_DYN if name.endswith("q") else L.BLUR_GENERIC
         fn = lambda: L.check(lib.b200img_gaussian_blur_batch_dev(src.data_ptr(), 3840, 2160, 3, L.U8, dst.data_ptr(), n, C.byref(p.raw), path, 0, st))
+elif name == "k3":
+    npx = 8192 * 8192
+    a16 = torch.randint(0, 65536, (npx, 4), dtype=torch.int32, device=dev, generator=g).to(torch.uint16)
+    o8 = torch.empty((npx, 3), dtype=torch.uint8, device=dev)
+    a8 = torch.randint(0, 256, (npx, 3), dtype=torch.uint8, device=dev, generator=g)
+    of = torch.empty((npx, 4), dtype=torch.float32, device=dev)
+    bg = torch.randint(0, 256, (npx, 4), dtype=torch.uint8, device=dev, generator=g)
+
+    def fn():
+        L.check(lib.b200img_convert_dev(a16.data_ptr(), L.U16, 4, o8.data_ptr(), L.U8, 3, npx, L.CAST, None, st))
+        L.check(lib.b200img_convert_dev(a8.data_ptr(), L.U8, 3, of.data_ptr(), L.F32, 4, npx, L.CAST, None, st))
+        L.check(lib.b200img_swizzle_02_dev(bg.data_ptr(), L.U8, 4, npx * 4, st))
 else:
     raise SystemExit(f"unknown workload {name}")
 for _ in range(reps):
